@@ -1,0 +1,151 @@
+/*
+ * kssd_b200.h -- C-ABI of libkssd_b200.so: the B200 (sm_100a) implementation of RabbitKSSD's two
+ * data-parallel hot paths.  Plain pointers and sizes only; no C++/torch types.
+ *
+ * The reference has no FFI layer: its seam is five free C++ functions.  The host shims under
+ * rabbitkssd_b200/csrc/host/ keep those five signatures and call the entry points below; each entry point
+ * cites the reference code it replaces (paths relative to the RabbitKSSD tree).
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error (KSSD_E_*); text via kssd_b200_last_error().  The
+ *    library never calls exit(); there is NO CPU fallback: without a usable CUDA device init fails.
+ *  - one kssd_ctx per GPU (one process or one host thread per GPU); a ctx is not thread-safe.
+ *  - pointers are HOST pointers unless the parameter is named d_* or the call ends in _device.
+ *  - hashes are uint32 (the reference's 32-bit path, half_k - drlevel <= 8, sketch.cpp:336); the 64-bit
+ *    path is reported as KSSD_E_UNSUPPORTED.
+ */
+#ifndef KSSD_B200_H
+#define KSSD_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KSSD_OK 0
+#define KSSD_E_CUDA (-1)        /* CUDA runtime error (text has the cudaError string) */
+#define KSSD_E_ARG (-2)         /* bad argument / call order */
+#define KSSD_E_UNSUPPORTED (-3) /* configuration the library does not implement (64-bit hashes) */
+#define KSSD_E_PARAM (-4)       /* half_subk - drlevel < 3: the reference aborts here (common.cpp:37-39) */
+#define KSSD_E_OVERFLOW (-5)    /* an output buffer was too small; text says which and the size needed */
+
+typedef struct kssd_ctx kssd_ctx;
+
+const char *kssd_b200_last_error(void);
+int kssd_b200_version(void);
+
+/* Create a context on CUDA device `device`.  Fails (KSSD_E_CUDA) when no device is usable. */
+int kssd_b200_init(kssd_ctx **ctx, int device);
+void kssd_b200_destroy(kssd_ctx *ctx);
+/* Run all work of this ctx on the caller's cudaStream_t (e.g. torch's current stream); NULL = own stream. */
+int kssd_b200_set_stream(kssd_ctx *ctx, void *cuda_stream);
+int kssd_b200_sync(kssd_ctx *ctx);
+
+/* ---- parameters + shuffle table --------------------------------------------------------------------
+ * replaces initParameter (src/common.cpp:35-78) and the retained-subset map build (src/sketch.cpp:338-345,
+ * :616-623).  shuffled_dim = the 16^half_subk ints of the .shuf file (src/shuffle.cpp:8-23), borrowed for
+ * the call.  Uploads the masks, a symmetrised membership bitmap and the exact retained-subset table. */
+int kssd_b200_set_params(kssd_ctx *ctx, int half_k, int half_subk, int drlevel, const int32_t *shuffled_dim);
+
+/* ---- sketching --------------------------------------------------------------------------------------
+ * replaces the per-base scan + per-genome set of sketchFastaFile / sketchFastqFile and the consumer tasks
+ * (src/sketch.cpp:173-314, :487-550, :777-849).  Input is PARSED sequence (no FASTA/FASTQ syntax): a flat
+ * byte buffer in which the records of one genome are separated by at least one non-ACGT byte (a separator
+ * resets the valid-run counter exactly as a new record does, sketch.cpp:487-488), cut into segments; segment
+ * i = bytes [seg_off[i], seg_off[i+1]) and belongs to genome seg_genome[i] (index in [0, n_genomes)).
+ * The first byte after a genome's last record must also be a separator (or the end of the batch).
+ * A record continued from the previous batch is prefixed by its last 2*half_k-1 bytes and first_emit is set
+ * to that count: k-mers ending before first_emit are context only. */
+typedef struct kssd_batch {
+    uint8_t *seq;         /* pinned, library owned, capacity bytes */
+    uint8_t *qual;        /* pinned, same layout; used only when the session was begun with has_qual */
+    uint64_t capacity;    /* bytes available in seq / qual */
+    uint64_t n_bytes;     /* filled by caller */
+    uint64_t *seg_off;    /* pinned, seg_capacity+1 entries; filled by caller, seg_off[0] == 0 */
+    uint32_t *seg_genome; /* pinned, seg_capacity entries; filled by caller */
+    uint32_t seg_capacity;
+    uint32_t n_seg;       /* filled by caller */
+    uint64_t first_emit;  /* filled by caller (0 when nothing is continued) */
+    void *priv;
+} kssd_batch;
+
+/* Start a sketch session for n_genomes genomes.  least_qual / least_num_kmer are the -Q / -n options
+ * (raw ASCII compare quality[i] >= least_qual, sketch.cpp:280; keep hashes seen >= least_num_kmer times,
+ * sketch.cpp:704-706); has_qual = 0 for FASTA. */
+int kssd_b200_sketch_begin(kssd_ctx *ctx, uint32_t n_genomes, int has_qual, int least_qual, int least_num_kmer);
+/* Double-buffered pinned staging: acquire blocks until one of the ctx's batches is free. */
+int kssd_b200_batch_acquire(kssd_ctx *ctx, kssd_batch **batch, uint64_t min_capacity, uint32_t min_segments);
+/* Async H2D + scan kernel; the batch may be re-acquired once the copy has drained. */
+int kssd_b200_batch_submit(kssd_ctx *ctx, kssd_batch *batch);
+/* Same scan on a buffer ALREADY resident in device memory (bench `value`, multi-GPU pipelines). d_seq must be
+ * 16-byte aligned; d_seg_off/d_seg_genome are device arrays. */
+int kssd_b200_sketch_scan_device(kssd_ctx *ctx, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
+                                 const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg,
+                                 uint64_t first_emit);
+/* Per-genome sort + unique (+ count filter): hashes[genome_off[g] .. genome_off[g+1]) ascending, unique.
+ * Host arrays are library owned and valid until the next sketch_begin / destroy. */
+int kssd_b200_sketch_finish(kssd_ctx *ctx, const uint32_t **hashes, const uint64_t **genome_off);
+/* Same, results stay in device memory (library owned). */
+int kssd_b200_sketch_finish_device(kssd_ctx *ctx, const uint32_t **d_hashes, const uint64_t **d_genome_off,
+                                   uint64_t *total);
+
+/* ---- inverted index -----------------------------------------------------------------------------------
+ * replaces transSketches, 32-bit path (src/sketch.cpp:970-1017): hash -> ascending genome ids.  The index is
+ * kept in device memory as CSR over the DISTINCT hashes.  index_export gives the host the content of the
+ * two files: dict = the .dict payload; (uniq_hash, uniq_count) = the non-zero entries of the .index count
+ * array (the host shim scatters them into the dense 2^(4(k-l)) array the file format wants). */
+#define KSSD_PTR_HOST 0
+#define KSSD_PTR_DEVICE 1
+int kssd_b200_index_build(kssd_ctx *ctx, const uint32_t *hashes, const uint64_t *genome_off, uint32_t n_genomes,
+                          int ptr_kind);
+int kssd_b200_index_export(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, const uint32_t **uniq_hash,
+                           const uint32_t **uniq_count, const uint32_t **dict);
+/* replaces the .index/.dict load + prefix sum of index_tridist / index_dist (src/dist.cpp:83-130, :488-523):
+ * counts = the dense count array of the .index file (hash_size entries), dict = the .dict payload. */
+int kssd_b200_index_load(kssd_ctx *ctx, uint64_t hash_size, const uint32_t *counts, const uint32_t *dict,
+                         uint64_t total, const uint32_t *ref_sizes, uint32_t n_ref);
+/* Device views of the CSR index (for replication to other GPUs with one NCCL broadcast). */
+int kssd_b200_index_device_views(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, uint32_t *n_ref,
+                                 const uint32_t **d_uniq_hash, const uint64_t **d_uniq_off,
+                                 const uint32_t **d_dict, const uint32_t **d_ref_sizes);
+/* Adopt a replicated index: device arrays are COPIED into ctx-owned memory. */
+int kssd_b200_index_adopt_device(kssd_ctx *ctx, uint64_t n_uniq, uint64_t total, uint32_t n_ref,
+                                 const uint32_t *d_uniq_hash, const uint64_t *d_uniq_off, const uint32_t *d_dict,
+                                 const uint32_t *d_ref_sizes);
+
+/* ---- distances ----------------------------------------------------------------------------------------
+ * replaces the per-row posting accumulation + row epilogue of index_tridist (src/dist.cpp:174-258) and
+ * index_dist (src/dist.cpp:560-692).  Query rows [row_begin,row_end) of the given query sketches are run
+ * against the loaded index (query-row sharding across GPUs).  A hit is a cell whose distance
+ * passes max_dist under a CONSERVATIVE device-side test; the caller recomputes Jaccard/containment and the
+ * distance with the reference's exact double expressions (dist.cpp:216-232, :237-251) for the final
+ * keep/drop, which makes the pair set and the printed numbers identical by construction.
+ *   triangle = 1: alldist, only cols > row (dist.cpp:207), strict  `<`  (dist.cpp:232);
+ *   triangle = 0: dist, all cols, inclusive `<=` (dist.cpp:624). */
+typedef struct kssd_hit { uint32_t row, col, common; } kssd_hit;
+typedef int (*kssd_sink)(void *user, const kssd_hit *hits, size_t n);
+int kssd_b200_dist_rows(kssd_ctx *ctx, const uint32_t *q_hashes, const uint64_t *q_off, uint32_t n_query,
+                        int ptr_kind, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size,
+                        double max_dist, int containment, kssd_sink sink, void *user);
+/* Same, hits stay in device memory (library owned until the next call); *n_hits = number written. */
+int kssd_b200_dist_rows_device(kssd_ctx *ctx, const uint32_t *d_q_hashes, const uint64_t *d_q_off,
+                               uint32_t n_query, uint32_t row_begin, uint32_t row_end, int triangle,
+                               int kmer_size, double max_dist, int containment, const kssd_hit **d_hits,
+                               uint64_t *n_hits);
+
+/* ---- introspection for bench.py / tests ---------------------------------------------------------------- */
+/* Bracket the scan / count kernels with CUDA events on the ctx stream (off by default). */
+int kssd_b200_set_profiling(kssd_ctx *ctx, int on);
+/* Number of kernels this ctx has launched since init (bench.py's gpu_launches). */
+uint64_t kssd_b200_launch_count(kssd_ctx *ctx);
+/* Time (ms, CUDA events on the ctx stream) and launch count of the scan kernel since the last call. */
+int kssd_b200_scan_kernel_time(kssd_ctx *ctx, double *ms, uint64_t *launches, uint64_t *bytes);
+/* Posting-accumulate kernel: time, launches, posting entries streamed, smem atomic increments. */
+int kssd_b200_count_kernel_time(kssd_ctx *ctx, double *ms, uint64_t *launches, uint64_t *postings,
+                                uint64_t *atomics);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KSSD_B200_H */

@@ -1,0 +1,226 @@
+"""Host-side Python mirror of the hot-path interface, over the C-ABI (ctypes).  Used by tests and bench.py; the
+C++ drop-in shims live in csrc/host/.  numpy arrays in, numpy arrays out; *_device variants take raw device
+pointers (e.g. torch tensors' data_ptr()) and leave results in device memory."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+
+def _np_from_ptr(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(C.addressof(ptr.contents))
+    return np.frombuffer(buf, dtype=dtype, count=n).copy()
+
+
+class Context:
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        self.h = C.c_void_p()
+        check(self.lib.kssd_b200_init(C.byref(self.h), device))
+        self.params = None
+        self.n_genomes = 0
+
+    def close(self):
+        if self.h:
+            self.lib.kssd_b200_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing ----
+    def set_stream(self, cuda_stream_ptr):
+        check(self.lib.kssd_b200_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        check(self.lib.kssd_b200_sync(self.h))
+
+    def set_profiling(self, on=True):
+        check(self.lib.kssd_b200_set_profiling(self.h, int(on)))
+
+    def launch_count(self):
+        return int(self.lib.kssd_b200_launch_count(self.h))
+
+    def scan_kernel_time(self):
+        ms, n, b = C.c_double(), C.c_uint64(), C.c_uint64()
+        check(self.lib.kssd_b200_scan_kernel_time(self.h, C.byref(ms), C.byref(n), C.byref(b)))
+        return ms.value, n.value, b.value
+
+    def count_kernel_time(self):
+        ms, n, p, a = C.c_double(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(self.lib.kssd_b200_count_kernel_time(self.h, C.byref(ms), C.byref(n), C.byref(p), C.byref(a)))
+        return ms.value, n.value, p.value, a.value
+
+    # ---- parameters ----
+    def set_params(self, half_k, half_subk, drlevel, shuffled_dim):
+        dim = np.ascontiguousarray(shuffled_dim, dtype=np.int32)
+        if half_subk < 8 and len(dim) != 1 << (4 * half_subk):
+            raise ValueError("shuffled_dim must have 16^half_subk entries")
+        check(self.lib.kssd_b200_set_params(self.h, half_k, half_subk, drlevel, dim.ctypes.data_as(_lib.i32p)))
+        self.params = (half_k, half_subk, drlevel)
+
+    # ---- sketching ----
+    def sketch_begin(self, n_genomes, has_qual=False, least_qual=0, least_num_kmer=1):
+        check(self.lib.kssd_b200_sketch_begin(self.h, n_genomes, int(has_qual), least_qual, least_num_kmer))
+        self.n_genomes = n_genomes
+
+    def submit_host(self, seq, seg_off, seg_genome, qual=None, first_emit=0):
+        """One pinned batch: copies the arrays into a library-owned pinned batch and submits it (async)."""
+        seq = np.ascontiguousarray(seq, dtype=np.uint8)
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)
+        seg_genome = np.ascontiguousarray(seg_genome, dtype=np.uint32)
+        b = C.POINTER(_lib.Batch)()
+        check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), len(seq), len(seg_genome)))
+        bt = b.contents
+        C.memmove(bt.seq, seq.ctypes.data, len(seq))
+        if qual is not None:
+            q = np.ascontiguousarray(qual, dtype=np.uint8)
+            C.memmove(bt.qual, q.ctypes.data, len(q))
+        C.memmove(bt.seg_off, seg_off.ctypes.data, seg_off.nbytes)
+        C.memmove(bt.seg_genome, seg_genome.ctypes.data, seg_genome.nbytes)
+        bt.n_bytes = len(seq)
+        bt.n_seg = len(seg_genome)
+        bt.first_emit = first_emit
+        check(self.lib.kssd_b200_batch_submit(self.h, b))
+
+    def acquire_batch(self, min_capacity, min_segments):
+        b = C.POINTER(_lib.Batch)()
+        check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), min_capacity, min_segments))
+        return b
+
+    def submit_batch(self, b):
+        check(self.lib.kssd_b200_batch_submit(self.h, b))
+
+    def scan_device(self, d_seq, n_bytes, d_seg_off, d_seg_genome, n_seg, d_qual=0, first_emit=0):
+        check(self.lib.kssd_b200_sketch_scan_device(self.h, C.c_void_p(d_seq), C.c_void_p(d_qual), n_bytes,
+                                                    C.c_void_p(d_seg_off), C.c_void_p(d_seg_genome), n_seg, first_emit))
+
+    def sketch_finish(self):
+        """-> (hashes uint32[total], genome_off uint64[n_genomes+1]) on the host; per genome sorted unique."""
+        hp, op = _lib.u32p(), _lib.u64p()
+        check(self.lib.kssd_b200_sketch_finish(self.h, C.byref(hp), C.byref(op)))
+        off = _np_from_ptr(op, self.n_genomes + 1, np.uint64)
+        return _np_from_ptr(hp, int(off[-1]), np.uint32), off
+
+    def sketch_finish_device(self):
+        """-> (d_hashes ptr, d_genome_off ptr, total); library-owned device memory."""
+        hp, op, tot = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        check(self.lib.kssd_b200_sketch_finish_device(self.h, C.byref(hp), C.byref(op), C.byref(tot)))
+        return hp.value or 0, op.value or 0, tot.value
+
+    def sketch(self, seq, genome_off, qual=None, least_qual=0, least_num_kmer=1, batch_bytes=None):
+        """Sketch a packed batch (rabbitkssd_b200.synth.pack_batch layout) through pinned host batches.
+        genome_off[n+1]: byte offsets; genome g owns [genome_off[g], genome_off[g+1]).  Large inputs are cut into
+        batches of ~batch_bytes at genome boundaries."""
+        genome_off = np.ascontiguousarray(genome_off, dtype=np.uint64)
+        n = len(genome_off) - 1
+        self.sketch_begin(n, qual is not None, least_qual, least_num_kmer)
+        if batch_bytes is None:
+            batch_bytes = 256 << 20
+        g = 0
+        while g < n:
+            g1 = g + 1
+            while g1 < n and int(genome_off[g1 + 1]) - int(genome_off[g]) <= batch_bytes:
+                g1 += 1
+            b0, b1 = int(genome_off[g]), int(genome_off[g1])
+            so = (genome_off[g:g1 + 1] - genome_off[g]).astype(np.uint64)
+            self.submit_host(seq[b0:b1], so, np.arange(g, g1, dtype=np.uint32), None if qual is None else qual[b0:b1])
+            g = g1
+        return self.sketch_finish()
+
+    # ---- index ----
+    def index_build(self, hashes, genome_off):
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint32)
+        genome_off = np.ascontiguousarray(genome_off, dtype=np.uint64)
+        check(self.lib.kssd_b200_index_build(self.h, C.c_void_p(hashes.ctypes.data), C.c_void_p(genome_off.ctypes.data),
+                                             len(genome_off) - 1, 0))
+
+    def index_build_device(self, d_hashes, d_genome_off, n_genomes):
+        check(self.lib.kssd_b200_index_build(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1))
+
+    def index_export(self):
+        """-> (uniq_hash u32[U], uniq_count u32[U], dict u32[P])"""
+        U, P = C.c_uint64(), C.c_uint64()
+        uh, uc, dc = _lib.u32p(), _lib.u32p(), _lib.u32p()
+        check(self.lib.kssd_b200_index_export(self.h, C.byref(U), C.byref(P), C.byref(uh), C.byref(uc), C.byref(dc)))
+        return (_np_from_ptr(uh, U.value, np.uint32), _np_from_ptr(uc, U.value, np.uint32),
+                _np_from_ptr(dc, P.value, np.uint32))
+
+    def index_load(self, counts, postings, ref_sizes):
+        counts = np.ascontiguousarray(counts, dtype=np.uint32)
+        postings = np.ascontiguousarray(postings, dtype=np.uint32)
+        ref_sizes = np.ascontiguousarray(ref_sizes, dtype=np.uint32)
+        check(self.lib.kssd_b200_index_load(self.h, len(counts), counts.ctypes.data_as(_lib.u32p),
+                                            postings.ctypes.data_as(_lib.u32p), len(postings),
+                                            ref_sizes.ctypes.data_as(_lib.u32p), len(ref_sizes)))
+
+    def index_device_views(self):
+        U, P, N = C.c_uint64(), C.c_uint64(), C.c_uint32()
+        a, b, c_, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(self.lib.kssd_b200_index_device_views(self.h, C.byref(U), C.byref(P), C.byref(N), C.byref(a), C.byref(b),
+                                                    C.byref(c_), C.byref(d)))
+        return dict(n_uniq=U.value, total=P.value, n_ref=N.value, d_uniq_hash=a.value, d_uniq_off=b.value,
+                    d_dict=c_.value, d_ref_sizes=d.value)
+
+    def index_adopt_device(self, n_uniq, total, n_ref, d_uniq_hash, d_uniq_off, d_dict, d_ref_sizes):
+        check(self.lib.kssd_b200_index_adopt_device(self.h, n_uniq, total, n_ref, C.c_void_p(d_uniq_hash),
+                                                    C.c_void_p(d_uniq_off), C.c_void_p(d_dict), C.c_void_p(d_ref_sizes)))
+
+    # ---- distances ----
+    def dist_rows(self, q_hashes, q_off, triangle, kmer_size, max_dist, containment=0, rows=None):
+        """-> structured hits (row, col, common) that pass the device's conservative test (host refines)."""
+        q_hashes = np.ascontiguousarray(q_hashes, dtype=np.uint32)
+        q_off = np.ascontiguousarray(q_off, dtype=np.uint64)
+        nq = len(q_off) - 1
+        r0, r1 = (0, nq) if rows is None else rows
+        chunks = []
+
+        def sink(user, hits, n):
+            arr = np.frombuffer((C.c_char * (n * 12)).from_address(C.addressof(hits.contents)), dtype=np.uint32)
+            chunks.append(arr.reshape(-1, 3).copy())
+            return 0
+
+        cb = _lib.SINK(sink)
+        check(self.lib.kssd_b200_dist_rows(self.h, C.c_void_p(q_hashes.ctypes.data), C.c_void_p(q_off.ctypes.data), nq, 0,
+                                           r0, r1, int(triangle), kmer_size, float(max_dist), int(containment), cb, None))
+        if not chunks:
+            return np.zeros((0, 3), dtype=np.uint32)
+        return np.concatenate(chunks)
+
+    def dist_rows_device(self, d_q_hashes, d_q_off, n_query, triangle, kmer_size, max_dist, containment=0, rows=None):
+        r0, r1 = (0, n_query) if rows is None else rows
+        hp, n = C.c_void_p(), C.c_uint64()
+        check(self.lib.kssd_b200_dist_rows_device(self.h, C.c_void_p(d_q_hashes), C.c_void_p(d_q_off), n_query, r0, r1,
+                                                  int(triangle), kmer_size, float(max_dist), int(containment),
+                                                  C.byref(hp), C.byref(n)))
+        return hp.value or 0, n.value
+
+
+def refine_hits(hits, row_sizes, col_sizes, kmer_size, max_dist, triangle, containment=0):
+    """Final keep/drop with the reference's exact double expressions (src/dist.cpp:216-232, :237-251; strict '<'
+    for alldist :232, '<=' for dist :624).  numpy's log is the same libm log the reference calls.
+    Returns (hits_kept, jorc, dist)."""
+    if len(hits) == 0:
+        return hits, np.zeros(0), np.zeros(0)
+    c = hits[:, 2].astype(np.int64)
+    s_row = np.asarray(row_sizes, dtype=np.int64)[hits[:, 0]]
+    s_col = np.asarray(col_sizes, dtype=np.int64)[hits[:, 1]]
+    empty = (s_row == 0) | (s_col == 0)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        if not containment:
+            v = np.where(empty, 0.0, c / (s_row + s_col - c).astype(np.float64))
+            arg = (2 * v) / (1.0 + v)
+        else:
+            v = np.where(empty, 0.0, c / np.minimum(s_row, s_col).astype(np.float64))
+            arg = v
+        import math
+        d = np.array([0.0 if x == 1.0 else 1.0 if x == 0.0 else -1.0 / kmer_size * math.log(a) for x, a in zip(v, arg)])
+    keep = d < max_dist if triangle else d <= max_dist
+    return hits[keep], v[keep], d[keep]

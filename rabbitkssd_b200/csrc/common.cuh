@@ -1,0 +1,145 @@
+// Internal declarations shared by the translation units of libkssd_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/kssd_b200.h"
+
+namespace kssd {
+
+void set_error(const char *fmt, ...);
+
+#define KSSD_CUDA(call)                                                                              \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess) {                                                                    \
+            kssd::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));  \
+            return KSSD_E_CUDA;                                                                      \
+        }                                                                                            \
+    } while (0)
+
+#define KSSD_TRY(call)               \
+    do {                             \
+        int r__ = (call);            \
+        if (r__ != KSSD_OK) return r__; \
+    } while (0)
+
+// Device buffer that only grows (HBM is plentiful: 180 GB per GPU; reallocation is the cost to avoid).
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes, cudaStream_t st, bool keep = false);
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct HostBuf {  // pinned
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// Scan-kernel parameters derived from (half_k, half_subk, drlevel); reference: src/common.cpp:35-78.
+struct ScanParams {
+    int half_k, half_subk, drlevel;
+    int hoc;          // half_outctx_len = half_k - half_subk
+    int kmer_size;    // 2*half_k
+    int nb;           // bases of the 2s-mer used as membership-bitmap index (<= 10)
+    int wbits;        // bitmap word-index bits = 2*nb - 5
+    uint64_t tupmask, domask, undomask0, undomask1;
+    uint32_t table_mask;  // exact table capacity - 1
+    int table_shift;      // 32 - log2(capacity)
+    int dim_end;
+};
+
+struct TimedLaunches {
+    std::vector<cudaEvent_t> ev;  // pairs
+    std::vector<cudaEvent_t> pool;
+    uint64_t launches = 0, units_a = 0, units_b = 0;
+    int begin(cudaStream_t st);
+    int end(cudaStream_t st);
+    int collect(double *ms);  // syncs the recorded events, recycles them
+};
+
+}  // namespace kssd
+
+struct kssd_batch_priv {
+    cudaEvent_t h2d_done;
+    bool in_flight = false;
+    kssd::HostBuf seq, qual, seg_off, seg_genome;
+};
+
+struct kssd_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    cudaStream_t copy_stream = nullptr;
+    uint64_t launches = 0;
+    bool profiling = false;
+
+    // parameters + tables
+    bool have_params = false;
+    kssd::ScanParams sp;
+    kssd::DevBuf d_bitmap, d_tab_keys, d_tab_vals;
+
+    // sketch session
+    bool in_session = false;
+    uint32_t n_genomes = 0;
+    int has_qual = 0, least_qual = 0, least_num_kmer = 1;
+    uint64_t bases_submitted = 0;
+    kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
+    uint64_t emit_cap = 0;
+    kssd::DevBuf d_cursor;    // u64 cursor (+ spare words)
+    kssd::DevBuf d_stage_seq[2], d_stage_qual[2], d_stage_segoff[2], d_stage_seggen[2];
+    cudaEvent_t stage_free[2] = {nullptr, nullptr};
+    int stage_next = 0;
+    kssd_batch batches[2];
+    kssd_batch_priv bpriv[2];
+    bool batches_init = false;
+    int batch_next = 0;
+    kssd::DevBuf d_sort_tmp, d_sort_counts, d_keys_unique;
+    kssd::DevBuf d_hashes, d_genome_off;
+    kssd::HostBuf h_hashes, h_genome_off, h_scalar;
+    uint64_t sketch_total = 0;
+
+    // index (CSR over distinct hashes)
+    bool have_index = false;
+    uint64_t n_uniq = 0, n_post = 0;
+    uint32_t n_ref = 0;
+    uint32_t max_ref_size = 0;
+    kssd::DevBuf d_uniq_hash, d_uniq_off, d_dict, d_ref_sizes, d_pairs, d_pairs_tmp;
+    kssd::HostBuf h_uniq_hash, h_uniq_count, h_dict;
+
+    // distances
+    kssd::DevBuf d_q_hashes, d_q_off, d_q_list_begin, d_q_list_end, d_hits, d_hit_cursor, d_rowwork;
+    kssd::HostBuf h_hits;
+
+    kssd::TimedLaunches t_scan, t_count;
+};
+
+namespace kssd {
+// sketch.cu
+int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
+                const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit);
+int build_tables(kssd_ctx *c, const int32_t *shuffled_dim);
+// radix.cu
+int radix_sort_u64(kssd_ctx *c, uint64_t *d_keys, uint64_t *d_tmp, uint64_t n, int lo_bits_begin, int lo_bits_end,
+                   int hi_bits_begin, int hi_bits_end, uint64_t **d_sorted);
+int unique_keys(kssd_ctx *c, const uint64_t *d_sorted, uint64_t n, int min_count, uint64_t *d_out_keys,
+                uint64_t *n_out);
+int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_genomes, uint32_t *d_hashes,
+                  uint64_t *d_genome_off);
+// index.cu
+int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
+                       uint64_t total);
+// dist.cu
+int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
+                     uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
+                     int containment, uint64_t *n_hits);
+}  // namespace kssd

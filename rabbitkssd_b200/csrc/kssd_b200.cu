@@ -1,0 +1,7 @@
+// Unity translation unit of libkssd_b200.so: the kernels launch each other's helpers, and a single TU avoids
+// relocatable device code.  Build: see rabbitkssd_b200/build.py (nvcc -gencode arch=compute_100a,code=sm_100a).
+#include "sketch.cu"
+#include "radix.cu"
+#include "index.cu"
+#include "dist.cu"
+#include "capi.cu"

@@ -1,0 +1,184 @@
+"""GPU: the CUDA path through the C-ABI against (a) the reference binary's golden fixtures and (b) the oracle on
+seeded inputs -- bit-exact hash sets, index, intersection counts and passing pair sets."""
+import numpy as np
+import pytest
+
+import oracle
+import util
+from rabbitkssd_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+CASES = sorted(util.golden_meta().keys())
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = api.Context(0)
+    yield c
+    c.close()
+
+
+def _gpu_sketch(ctx, k, s, l, genomes, quals=None, least_qual=0, least_num_kmer=1, batch_bytes=None):
+    ctx.set_params(k, s, l, util.shuffled_dim(k, s, l))
+    seq, qual, off = synth.pack_batch(genomes, quals)
+    h, goff = ctx.sketch(seq, off, qual, least_qual, least_num_kmer, batch_bytes)
+    return [h[int(goff[g]):int(goff[g + 1])] for g in range(len(genomes))], h, goff
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_sketch_equals_reference_golden(ctx, case):
+    m = util.golden_meta()[case]
+    c = m["recipe"]
+    names, genomes, quals = util.case_genomes(case)
+    sets, _, _ = _gpu_sketch(ctx, c["k"], c["s"], c["l"], genomes, quals, c.get("Q", 0), c.get("n", 1))
+    z = util.golden_npz(case)
+    for n, s in zip(names, sets):
+        assert np.array_equal(s.astype(np.uint64), z["set_" + n]), n
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_index_and_distances_equal_reference_golden(ctx, case):
+    m = util.golden_meta()[case]
+    c = m["recipe"]
+    z = util.golden_npz(case)
+    names = m["names"]
+    sets = [z["set_" + n] for n in names]
+    h, off = util.flatten_sets(sets)
+    sizes = np.diff(off).astype(np.int64)
+    ctx.index_build(h, off)
+    uh, uc, dict_ = ctx.index_export()
+    assert np.array_equal(uh.astype(np.uint64), z["index_hash"])
+    assert np.array_equal(uc, z["index_count"])
+    o_dict, _, _, _ = oracle.index_build(h, off)
+    assert np.array_equal(dict_, o_dict)
+    for tag in ["alldist", "alldist_M1", "dist", "dist_M1", "dist_D1"]:
+        cont = 1 if tag.endswith("M1") else 0
+        D = 1.0 if tag.endswith("D1") else c["D"]
+        tri = tag.startswith("alldist")
+        hits = ctx.dist_rows(h, off, tri, 2 * c["k"], D, cont)
+        hits, jorc, d = api.refine_hits(hits, sizes, sizes, 2 * c["k"], D, tri, cont)
+        got = []
+        for (r, cl, cm), j_, d_ in zip(hits, jorc, d):
+            if tri:
+                got.append((names[cl], names[r], int(cm), int(sizes[r]), int(sizes[cl]), "%f" % j_, "%f" % d_))
+            else:
+                got.append((names[r], names[cl], int(cm), int(sizes[cl]), int(sizes[r]), "%f" % j_, "%f" % d_))
+        want = sorted(tuple(x) for x in m["lines"][tag])
+        assert sorted(got) == want, tag
+
+
+def test_index_load_from_reference_files_layout(ctx):
+    """index_load takes the dense count array + postings exactly as the reference's .index/.dict hold them."""
+    m = util.golden_meta()["fa_k9s6l3"]
+    z = util.golden_npz("fa_k9s6l3")
+    sets = [z["set_" + n] for n in m["names"]]
+    h, off = util.flatten_sets(sets)
+    sizes = np.diff(off).astype(np.uint32)
+    counts = np.zeros(m["hash_size"], dtype=np.uint32)
+    counts[z["index_hash"].astype(np.int64)] = z["index_count"]
+    o_dict, _, _, _ = oracle.index_build(h, off)
+    ctx.index_load(counts, o_dict, sizes)
+    hits = ctx.dist_rows(h, off, True, 18, 0.15)
+    hr, hc, hm = oracle.alldist(h, off, 18, 0.15)
+    hits, _, _ = api.refine_hits(hits, sizes, sizes, 18, 0.15, True)
+    o = np.lexsort((hits[:, 1], hits[:, 0]))
+    assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
+
+
+@pytest.mark.parametrize("k,s,l,length,n", [(10, 6, 3, 1200000, 6), (9, 6, 3, 700000, 5), (8, 5, 2, 90000, 7)])
+def test_sketch_equals_oracle_random(ctx, k, s, l, length, n):
+    fam = synth.family(777 + k * 10 + l, n, length, 0.03, n_contigs=3)
+    fam = [[synth.sprinkle(c, 5 + gi * 7 + ci, n_runs=8, run_len=7, lowercase_frac=0.03) for ci, c in enumerate(g)]
+           for gi, g in enumerate(fam)]
+    want = util.oracle_sketch(k, s, l, fam)
+    # small batch size => several pinned batches through the double buffer
+    got, _, _ = _gpu_sketch(ctx, k, s, l, fam, batch_bytes=max(length * 2, 1 << 20))
+    for g, (a, b) in enumerate(zip(got, want)):
+        assert np.array_equal(a.astype(np.uint64), b), g
+
+
+def test_sketch_edge_cases(ctx):
+    k, s, l = 10, 6, 3
+    base = synth.random_bases(4242, 300000)
+    genomes = [
+        [np.zeros(0, np.uint8)],                                   # empty genome
+        [base[:19]],                                               # shorter than one k-mer
+        [base[:20]],                                               # exactly one k-mer
+        [np.full(5000, ord("N"), np.uint8)],                       # nothing valid
+        [base[:100000], np.zeros(0, np.uint8), base[100000:100019], base[100019:]],  # ragged records
+        [np.concatenate([base[:50000], np.frombuffer(b"\xff\x80\x00*", np.uint8), base[50000:]])],  # bytes >= 0x80
+        [base],
+    ]
+    want = util.oracle_sketch(k, s, l, genomes)
+    got, _, _ = _gpu_sketch(ctx, k, s, l, genomes)
+    for g, (a, b) in enumerate(zip(got, want)):
+        assert np.array_equal(a.astype(np.uint64), b), g
+    assert len(got[0]) == 0 and len(got[1]) == 0 and len(got[3]) == 0
+
+
+def test_fastq_quality_and_count_filter(ctx):
+    k, s, l = 10, 6, 3
+    seq = synth.random_bases(99, 400000)
+    n_reads, rl = 9000, 150
+    r = synth.splitmix64(1234, n_reads)
+    starts = (r % np.uint64(len(seq) - rl)).astype(np.int64)
+    reads = [seq[a:a + rl] for a in starts]
+    quals = [((synth.splitmix64(555 + i, rl) % np.uint64(41)) + 33).astype(np.uint8) for i in range(n_reads)]
+    for Q, n in [(0, 1), (40, 1), (38, 2), (50, 3)]:
+        want = util.oracle_sketch(k, s, l, [reads], [quals], Q, n)
+        got, _, _ = _gpu_sketch(ctx, k, s, l, [reads], [quals], Q, n)
+        assert np.array_equal(got[0].astype(np.uint64), want[0]), (Q, n)
+
+
+@pytest.mark.parametrize("containment", [0, 1])
+def test_alldist_equals_oracle_synthetic_sketches(ctx, containment):
+    h, off = synth.synth_sketches(31337, 150, 10, 300, 28)
+    sizes = np.diff(off).astype(np.int64)
+    ctx.index_build(h, off)
+    hits = ctx.dist_rows(h, off, True, 20, 0.05, containment)
+    hits, _, _ = api.refine_hits(hits, sizes, sizes, 20, 0.05, True, containment)
+    hr, hc, hm = oracle.alldist(h, off, 20, 0.05, containment)
+    o = np.lexsort((hits[:, 1], hits[:, 0]))
+    assert len(hr) > 100
+    assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
+
+
+def test_dist_row_sharding_equals_oracle(ctx):
+    rh, roff = synth.synth_sketches(2024, 120, 10, 250, 24)
+    qh, qoff = synth.synth_sketches(2024, 120, 3, 250, 24, survival_step=0.1)  # same roots, other members
+    rs, qs = np.diff(roff).astype(np.int64), np.diff(qoff).astype(np.int64)
+    ctx.index_build(rh, roff)
+    nq = len(qoff) - 1
+    parts = []
+    for lo, hi in [(0, nq // 3), (nq // 3, nq // 2), (nq // 2, nq)]:  # three "GPUs"
+        parts.append(ctx.dist_rows(qh, qoff, False, 18, 0.08, 0, rows=(lo, hi)))
+    hits = np.concatenate(parts)
+    hits, _, _ = api.refine_hits(hits, qs, rs, 18, 0.08, False)
+    hr, hc, hm = oracle.dist(qh, qoff, rh, roff, 18, 0.08)
+    o = np.lexsort((hits[:, 1], hits[:, 0]))
+    assert len(hr) > 50
+    assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
+
+
+def test_full_size_properties_c1(ctx):
+    """BASELINE config 1 shape (100 x 5 Mbp is too slow for the oracle in a unit test: 12 x 5 Mbp here, oracle on 3)
+    plus size-independent properties: sorted, unique, idempotent, reverse-complement invariant."""
+    k, s, l = 10, 6, 3
+    fam = synth.family(20261104, 12, 5000000, 0.04, n_contigs=2)
+    sets, h, goff = _gpu_sketch(ctx, k, s, l, fam)
+    for x in sets:
+        assert np.all(np.diff(x.astype(np.int64)) > 0)
+        assert abs(len(x) - 5000000 / 4096) < 200
+    want = util.oracle_sketch(k, s, l, fam[:3])
+    for a, b in zip(sets[:3], want):
+        assert np.array_equal(a.astype(np.uint64), b)
+    comp = np.zeros(256, np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    rc = [[comp[c[::-1]].copy() for c in g] for g in fam[:4]]
+    sets_rc, _, _ = _gpu_sketch(ctx, k, s, l, rc)
+    for a, b in zip(sets[:4], sets_rc):
+        assert np.array_equal(a, b)  # canonical k-mers: strand does not matter
+    sets2, _, _ = _gpu_sketch(ctx, k, s, l, fam[:4])
+    for a, b in zip(sets[:4], sets2):
+        assert np.array_equal(a, b)
