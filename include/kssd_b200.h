@@ -83,6 +83,13 @@ int kssd_b200_batch_submit(kssd_ctx *ctx, kssd_batch *batch);
 int kssd_b200_sketch_scan_device(kssd_ctx *ctx, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
                                  const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg,
                                  uint64_t first_emit);
+/* Same scan straight from the CALLER's host buffers (best pinned with cudaHostAlloc/cudaHostRegister: the copy
+ * is then asynchronous): the buffer is streamed H2D in chunk_bytes pieces (0 = 256 MiB) through the ctx's two
+ * staging buffers, copy of chunk i+1 overlapping the scan of chunk i; chunk borders carry a 32-byte context
+ * prefix so that no k-mer is lost or emitted twice.  seg_off / seg_genome as above, over the whole buffer. */
+int kssd_b200_sketch_scan_host(kssd_ctx *ctx, const uint8_t *seq, const uint8_t *qual, uint64_t n_bytes,
+                               const uint64_t *seg_off, const uint32_t *seg_genome, uint32_t n_seg,
+                               uint64_t chunk_bytes);
 /* Per-genome sort + unique (+ count filter): hashes[genome_off[g] .. genome_off[g+1]) ascending, unique.
  * Host arrays are library owned and valid until the next sketch_begin / destroy. */
 int kssd_b200_sketch_finish(kssd_ctx *ctx, const uint32_t **hashes, const uint64_t **genome_off);

@@ -40,6 +40,8 @@ SYMBOLS = {
     "kssd_b200_batch_submit": (C.c_int, [C.c_void_p, C.POINTER(Batch)]),
     "kssd_b200_sketch_scan_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                                C.c_uint32, C.c_uint64]),
+    "kssd_b200_sketch_scan_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                             C.c_uint32, C.c_uint64]),
     "kssd_b200_sketch_finish": (C.c_int, [C.c_void_p, C.POINTER(u32p), C.POINTER(u64p)]),
     "kssd_b200_sketch_finish_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), u64p]),
     "kssd_b200_index_build": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]),

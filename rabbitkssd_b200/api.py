@@ -102,6 +102,14 @@ class Context:
         check(self.lib.kssd_b200_sketch_scan_device(self.h, C.c_void_p(d_seq), C.c_void_p(d_qual), n_bytes,
                                                     C.c_void_p(d_seg_off), C.c_void_p(d_seg_genome), n_seg, first_emit))
 
+    def scan_host(self, seq_ptr, n_bytes, seg_off, seg_genome, qual_ptr=0, chunk_bytes=0):
+        """Stream a caller-owned (ideally pinned) host buffer through the double-buffered H2D pipeline."""
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)
+        seg_genome = np.ascontiguousarray(seg_genome, dtype=np.uint32)
+        check(self.lib.kssd_b200_sketch_scan_host(self.h, C.c_void_p(seq_ptr), C.c_void_p(qual_ptr), n_bytes,
+                                                  C.c_void_p(seg_off.ctypes.data), C.c_void_p(seg_genome.ctypes.data),
+                                                  len(seg_genome), chunk_bytes))
+
     def sketch_finish(self):
         """-> (hashes uint32[total], genome_off uint64[n_genomes+1]) on the host; per genome sorted unique."""
         hp, op = _lib.u32p(), _lib.u64p()

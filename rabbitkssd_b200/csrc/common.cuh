@@ -126,7 +126,8 @@ struct kssd_ctx {
 namespace kssd {
 // sketch.cu
 int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
-                const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit);
+                const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit,
+                uint64_t pos_base = 0);
 int build_tables(kssd_ctx *c, const int32_t *shuffled_dim);
 // radix.cu
 int radix_sort_u64(kssd_ctx *c, uint64_t *d_keys, uint64_t *d_tmp, uint64_t n, int lo_bits_begin, int lo_bits_end,

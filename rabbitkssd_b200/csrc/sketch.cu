@@ -28,6 +28,7 @@ struct ScanArgs {
     const uint32_t *seg_genome;
     uint32_t n_seg;
     uint64_t first_emit;
+    uint64_t pos_base;  // position of seq[0] in the coordinates of seg_off (chunked host submits)
     const uint32_t *bitmap;
     const uint32_t *tab_keys;
     const uint32_t *tab_vals;
@@ -111,6 +112,7 @@ __device__ __noinline__ void exact_emit(const ScanArgs &a, uint32_t W, uint32_t 
     if (pos < a.first_emit) return;
     uint64_t dr = (((uni & sp.undomask0) | ((uni & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | pf;
     // owning segment: largest s with seg_off[s] <= pos
+    pos += a.pos_base;
     uint32_t lo = 0, hi = a.n_seg;
     while (hi - lo > 1) {
         uint32_t mid = (lo + hi) >> 1;
@@ -332,7 +334,8 @@ static int launch_hoc(kssd_ctx *c, const ScanArgs &a, size_t smem) {
 }
 
 int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
-                const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit) {
+                const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit,
+                uint64_t pos_base) {
     if (n_bytes == 0 || n_seg == 0) return KSSD_OK;
     if ((reinterpret_cast<uintptr_t>(d_seq) & 15) || (d_qual && (reinterpret_cast<uintptr_t>(d_qual) & 15))) {
         set_error("sequence / quality device buffers must be 16-byte aligned");
@@ -345,6 +348,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.seg_genome = d_seg_genome;
     a.n_seg = n_seg;
     a.first_emit = first_emit;
+    a.pos_base = pos_base;
     a.bitmap = c->d_bitmap.as<uint32_t>();
     a.tab_keys = c->d_tab_keys.as<uint32_t>();
     a.tab_vals = c->d_tab_vals.as<uint32_t>();
