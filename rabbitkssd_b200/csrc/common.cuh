@@ -49,7 +49,8 @@ struct ScanParams {
     int half_k, half_subk, drlevel;
     int hoc;          // half_outctx_len = half_k - half_subk
     int kmer_size;    // 2*half_k
-    int nb;           // bases of the 2s-mer used as membership-bitmap index (<= 10)
+    int group;        // G: consecutive k-mer end positions decided by one bitmap test (1..4)
+    int nb;           // bases common to the G windows that index the membership bitmap (<= 10)
     int wbits;        // bitmap word-index bits = 2*nb - 5
     uint64_t tupmask, domask, undomask0, undomask1;
     uint32_t table_mask;  // exact table capacity - 1
