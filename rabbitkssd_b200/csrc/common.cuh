@@ -87,7 +87,7 @@ struct kssd_ctx {
     // parameters + tables
     bool have_params = false;
     kssd::ScanParams sp;
-    kssd::DevBuf d_bitmap, d_tab_keys, d_tab_vals;
+    kssd::DevBuf d_bitmap, d_tab_keys;  // membership bitmap, exact (dim_id<<32|value) table
 
     // sketch session
     bool in_session = false;

@@ -30,31 +30,30 @@ namespace kssd {
 struct ScanArgs {
     const uint8_t *seq;
     const uint8_t *qual;
-    uint64_t n_bytes;
-    const uint64_t *seg_off;
-    const uint32_t *seg_genome;
-    uint32_t n_seg;
-    uint64_t first_emit;
-    uint64_t pos_base;  // position of seq[0] in the coordinates of seg_off (chunked host submits)
-    const uint32_t *bitmap;
-    const uint32_t *tab_keys;
-    const uint32_t *tab_vals;
-    unsigned long long *emit;
+    uint32_t n_bytes;          // <= 2^31: launch_scan cuts larger buffers into pieces
+    uint32_t first_emit;       // k-mers ending before this byte are context only
+    const uint32_t *bitmap;    // membership bitmap (copied to shared memory)
+    const unsigned long long *table;  // exact retained-subset table: (dim_id << 32 | value), ~0 = empty
+    unsigned long long *emit;  // (position << 32 | hash); resolve_kernel turns positions into genome ids
     unsigned long long *cursor;
     uint64_t emit_cap;
-    uint64_t n_tiles;
+    uint32_t n_tiles;
+    uint32_t n_interior;       // tiles [1, n_interior) lie completely inside the buffer (halo included)
     uint32_t bitmap_words;
-    uint32_t addr_mask;  // ((1<<wbits)-1) << 2
-    int preshift;        // bit offset (mod 32) of the first index base of test 0 inside [P0,P1,A0,A1]
+    uint32_t addr_mask;        // ((1<<wbits)-1) << 2
+    int preshift;              // bit offset (mod 32) of the first index base of test 0 inside [P0,P1,A0,A1]
     int least_qual;
     ScanParams sp;
 };
 
 static constexpr int kScanThreads = 1024;
-static constexpr int kLaneBases = 32;                  // bases owned by a lane
-static constexpr int kTileLanes = 31;                  // lanes 1..31 own new bases, lane 0 is halo
-static constexpr int kQueueCap = 64;                   // per-warp candidate queue entries
-static constexpr int kWindowWords = 7;                 // 28 bytes >= 2k + G - 1 (k <= 12, G <= 4)
+static constexpr int kScanWarps = kScanThreads / 32;
+static constexpr int kLaneBases = 32;                          // bases owned by a lane
+static constexpr int kTileLanes = 31;                          // lanes 1..31 own new bases, lane 0 is halo
+static constexpr int kTileBytes = kTileLanes * kLaneBases;     // 992
+static constexpr int kQueueCap = 64;                           // per-warp candidate / output queue entries
+static constexpr int kWindowWords = 7;                         // 28 bytes >= 2k + G - 1 (k <= 12, G <= 4)
+static constexpr uint32_t kMaxPiece = 1u << 30;                // bytes per launch (positions are 32-bit)
 
 // ---- SWAR decode -----------------------------------------------------------------------------------------
 // filter encoding: bits 1-2 of the ASCII byte (A/a 0, C/c 1, T/t 2, G/g 3); 4 bytes -> 8 bits in the top byte,
@@ -88,16 +87,16 @@ __device__ __forceinline__ uint32_t nz4(uint32_t e) {
     return ((f >> 7) * 0x01020408u) >> 24 & 0xFu;
 }
 
-// 16-byte chunk c of the buffer; chunks outside [0, n_bytes) read as 0x00 (an invalid base)
-__device__ __forceinline__ uint4 load_chunk(const uint8_t *base, long long c, uint64_t n_bytes) {
+// 16 bytes at byte offset off (multiple of 16, may be negative); bytes outside [0, n_bytes) read as 0x00
+__device__ __forceinline__ uint4 load_chunk(const uint8_t *base, int off, uint32_t n_bytes) {
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (c >= 0) {
-        uint64_t b = (uint64_t)c * 16;
+    if (off >= 0) {
+        const uint32_t b = (uint32_t)off;
         if (b + 16 <= n_bytes) {
             v = __ldg(reinterpret_cast<const uint4 *>(base + b));
         } else if (b < n_bytes) {
             uint32_t w[4] = {0, 0, 0, 0};
-            for (int j = 0; j < 16 && b + j < n_bytes; j++) w[j >> 2] |= (uint32_t)base[b + j] << (8 * (j & 3));
+            for (uint32_t j = 0; j < 16 && b + j < n_bytes; j++) w[j >> 2] |= (uint32_t)base[b + j] << (8 * (j & 3));
             v = make_uint4(w[0], w[1], w[2], w[3]);
         }
     }
@@ -106,11 +105,17 @@ __device__ __forceinline__ uint4 load_chunk(const uint8_t *base, long long c, ui
 
 // 28 raw bytes starting at byte `start` (any alignment, may be negative): three aligned 128-bit loads and a
 // select network instead of byte loads.
-__device__ __forceinline__ void load_window(const uint8_t *base, long long start, uint64_t n_bytes, uint32_t (&w)[kWindowWords]) {
-    const long long c0 = start >> 4;  // floor
-    const uint4 v0 = load_chunk(base, c0, n_bytes), v1 = load_chunk(base, c0 + 1, n_bytes), v2 = load_chunk(base, c0 + 2, n_bytes);
+__device__ __forceinline__ void load_window(const uint8_t *base, int start, uint32_t n_bytes, uint32_t (&w)[kWindowWords]) {
+    const int a0 = start & ~15;  // floor to 16 (two's complement)
+    uint4 v0, v1, v2;
+    if (a0 >= 0 && (uint32_t)a0 + 48 <= n_bytes) {
+        const uint4 *p = reinterpret_cast<const uint4 *>(base + (uint32_t)a0);
+        v0 = __ldg(p); v1 = __ldg(p + 1); v2 = __ldg(p + 2);
+    } else {
+        v0 = load_chunk(base, a0, n_bytes); v1 = load_chunk(base, a0 + 16, n_bytes); v2 = load_chunk(base, a0 + 32, n_bytes);
+    }
     const uint32_t S[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
-    const int o = (int)(start - c0 * 16);
+    const int o = start - a0;
     const bool q2 = o & 8, q1 = o & 4;
     const int r8 = (o & 3) * 8;
     uint32_t T[kWindowWords + 2];
@@ -123,76 +128,83 @@ __device__ __forceinline__ void load_window(const uint8_t *base, long long start
     for (int i = 0; i < kWindowWords; i++) w[i] = __funnelshift_r(U[i], U[i + 1], r8);
 }
 
-__device__ __forceinline__ uint64_t revcomp_bits(uint64_t t, int bits) {
-    uint64_t r = __brevll(t);
+// complement-reverse of the 28 bases in c (first base most significant, 56 bits): base i lands at bits [2i, 2i+2)
+__device__ __forceinline__ uint64_t revcomp56(uint64_t c) {
+    uint64_t r = __brevll(c << 8);
     r = ((r >> 1) & 0x5555555555555555ull) | ((r & 0x5555555555555555ull) << 1);
-    r = ~r;
-    return r >> (64 - bits);
+    return ~r & 0x00FFFFFFFFFFFFFFull;
 }
 
-// Exact path for one queued group: k-mer end positions p0 .. p0+cnt-1 (buffer coordinates).
+// Exact path for one queued group: k-mer end positions p0 .. p0+cnt-1.  Returns in ok a bit per position whose
+// k-mer is retained (all reference conditions checked), hashes in dr[].
 template <int G>
-__device__ __noinline__ void exact_group(const ScanArgs &a, uint64_t p0) {
+__device__ __forceinline__ uint32_t exact_group(const ScanArgs &a, uint32_t p0, uint32_t (&dr)[G]) {
     const ScanParams &sp = a.sp;
     const int L = sp.kmer_size;
-    int cnt = kLaneBases - (int)(p0 & (kLaneBases - 1));
+    int cnt = kLaneBases - (int)(p0 % kLaneBases);
     if (cnt > G) cnt = G;
-    const long long start = (long long)p0 - (L - 1);
+    const int start = (int)p0 - (L - 1);
     uint32_t w[kWindowWords];
     load_window(a.seq, start, a.n_bytes, w);
     uint64_t C = 0;   // 2-bit codes of the 28 bytes, first byte most significant
-    uint32_t V = 0;   // bit i = byte i is a valid base
+    uint32_t E = 0;   // non-zero <=> some byte of the window is not a base
+    uint32_t err[kWindowWords];
 #pragma unroll
     for (int i = 0; i < kWindowWords; i++) {
-        uint32_t code, err;
-        decode4(w[i], code, err);
+        uint32_t code;
+        decode4(w[i], code, err[i]);
         C = (C << 8) | pack4_msb(code);
-        V |= (~nz4(err) & 0xFu) << (4 * i);
+        E |= err[i];
     }
-    const uint32_t lmask = (L >= 32) ? 0xFFFFFFFFu : ((1u << L) - 1u);
-    bool have_qual = false;
-    uint32_t QV = 0;
-    for (int j = 0; j < cnt; j++) {
-        if (((V >> j) & lmask) != lmask) continue;  // an invalid base inside the window (sketch.cpp:494-505)
-        const uint64_t pos = p0 + j;
-        if (pos < a.first_emit) continue;            // context of a continued record
-        const uint64_t tuple = (C >> (2 * (4 * kWindowWords - L - j))) & sp.tupmask;
-        const uint64_t rvs = revcomp_bits(tuple, 2 * L);
-        const uint64_t uni = tuple < rvs ? tuple : rvs;
-        const uint32_t dim_id = (uint32_t)((uni & sp.domask) >> (2 * sp.hoc));
-        uint32_t slot = (dim_id * 0x9E3779B1u) >> sp.table_shift;
-        uint32_t pf = 0;
-        bool found = false;
-        while (true) {
-            uint32_t k = __ldg(a.tab_keys + slot);
-            if (k == dim_id) { pf = __ldg(a.tab_vals + slot); found = true; break; }
-            if (k == 0xFFFFFFFFu) break;
-            slot = (slot + 1) & sp.table_mask;
-        }
-        if (!found) continue;
-        if (a.qual) {  // valid only if (signed char)quality >= least_qual (sketch.cpp:280), checked for survivors only
-            if (!have_qual) {
-                uint32_t qw[kWindowWords];
-                load_window(a.qual, start, a.n_bytes, qw);
-                const uint32_t lq4 = (uint32_t)(a.least_qual & 0xFF) * 0x01010101u;
+    const uint64_t R = revcomp56(C);
+    // probe the exact table for every position of the group; loads are independent
+    unsigned long long kv[G];
+    uint64_t uni[G];
+    uint32_t dim[G], slot[G];
 #pragma unroll
-                for (int i = 0; i < kWindowWords; i++) QV |= nz4(__vcmpges4(qw[i], lq4)) << (4 * i);
-                have_qual = true;
-            }
+    for (int j = 0; j < G; j++) {
+        const uint64_t tuple = (C >> (2 * (4 * kWindowWords - L - j))) & sp.tupmask;
+        const uint64_t rvs = (R >> (2 * j)) & sp.tupmask;
+        uni[j] = tuple < rvs ? tuple : rvs;
+        dim[j] = (uint32_t)((uni[j] & sp.domask) >> (2 * sp.hoc));
+        slot[j] = (dim[j] * 0x9E3779B1u) >> sp.table_shift;
+        kv[j] = __ldg(a.table + slot[j]);
+    }
+    uint32_t ok = 0;
+#pragma unroll
+    for (int j = 0; j < G; j++) {
+        dr[j] = 0;
+        if (kv[j] == ~0ull || j >= cnt) continue;  // empty slot: not retained (the common case)
+        // rare from here on: a retained dim_id or a hash collision
+        unsigned long long e = kv[j];
+        uint32_t s = slot[j];
+        while (e != ~0ull && (uint32_t)(e >> 32) != dim[j]) {
+            s = (s + 1) & sp.table_mask;
+            e = __ldg(a.table + s);
+        }
+        if (e == ~0ull) continue;
+        const uint32_t lmask = (1u << L) - 1u;  // L <= 24
+        if (E) {  // exact per-byte validity (sketch.cpp:494-505): every base of the window must be ACGTacgt
+            uint32_t V = 0;
+#pragma unroll
+            for (int i = 0; i < kWindowWords; i++) V |= (~nz4(err[i]) & 0xFu) << (4 * i);
+            if (((V >> j) & lmask) != lmask) continue;
+        }
+        if (p0 + j < a.first_emit) continue;  // context of a continued record
+        if (a.qual) {  // valid only if (signed char)quality >= least_qual (sketch.cpp:280); survivors only
+            uint32_t qw[kWindowWords];
+            load_window(a.qual, start, a.n_bytes, qw);
+            const uint32_t lq4 = (uint32_t)(a.least_qual & 0xFF) * 0x01010101u;
+            uint32_t QV = 0;
+#pragma unroll
+            for (int i = 0; i < kWindowWords; i++) QV |= nz4(__vcmpges4(qw[i], lq4)) << (4 * i);
             if (((QV >> j) & lmask) != lmask) continue;
         }
-        const uint64_t dr = (((uni & sp.undomask0) | ((uni & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | pf;
-        // owning segment: largest s with seg_off[s] <= pos
-        const uint64_t gpos = pos + a.pos_base;
-        uint32_t lo = 0, hi = a.n_seg;
-        while (hi - lo > 1) {
-            uint32_t mid = (lo + hi) >> 1;
-            if (a.seg_off[mid] <= gpos) lo = mid; else hi = mid;
-        }
-        const uint32_t g = a.seg_genome[lo];
-        const unsigned long long idx = atomicAdd(a.cursor, 1ull);
-        if (idx < a.emit_cap) a.emit[idx] = ((unsigned long long)g << 32) | (uint32_t)dr;
+        const uint64_t u = uni[j];
+        dr[j] = (uint32_t)((((u & sp.undomask0) | ((u & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | (uint32_t)e);
+        ok |= 1u << j;
     }
+    return ok;
 }
 
 // G: k-mer end positions decided per bitmap test.  W0: word offset (0/1) of the first index base of test 0.
@@ -211,28 +223,68 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     constexpr int T = (kLaneBases + G - 1) / G;  // tests per lane
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    unsigned long long *queue = reinterpret_cast<unsigned long long *>(s_mem + a.bitmap_words) + warp * kQueueCap;
-    const uint64_t warps_total = (uint64_t)gridDim.x * (blockDim.x >> 5);
+    uint32_t *cand_q = s_mem + a.bitmap_words + warp * kQueueCap;                                        // positions
+    unsigned long long *out_q = reinterpret_cast<unsigned long long *>(s_mem + a.bitmap_words + kScanWarps * kQueueCap) + warp * kQueueCap;
+    const uint32_t tile_stride = gridDim.x * kScanWarps;
     // interleave warps of different CTAs over consecutive tiles so that all SMs stream the same HBM region
-    uint64_t tile = (uint64_t)warp * gridDim.x + blockIdx.x;
+    uint32_t tile = (uint32_t)warp * gridDim.x + blockIdx.x;
     if (tile >= a.n_tiles) return;
     const uint32_t addr_mask = a.addr_mask;
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
     const uint32_t lt = (1u << lane) - 1u;
-    int qcount = 0;
+    const int lane_off = (lane - 1) * kLaneBases;
+    const uint8_t *lane_ptr = a.seq + lane_off;  // lane 0: before the tile (halo)
+    int n_cand = 0, n_out = 0;
 
-    long long c = ((long long)tile * kTileLanes + lane - 1) * 2;  // first 16-byte chunk of this lane
-    uint4 cur0 = load_chunk(a.seq, c, a.n_bytes), cur1 = load_chunk(a.seq, c + 1, a.n_bytes);
+    auto load_tile = [&](uint32_t tl, uint4 &v0, uint4 &v1) {
+        if (tl >= 1 && tl < a.n_interior) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(lane_ptr + (size_t)tl * kTileBytes);
+            v0 = __ldg(p);
+            v1 = __ldg(p + 1);
+        } else {
+            const int off = (int)(tl * kTileBytes) + lane_off;
+            v0 = load_chunk(a.seq, off, a.n_bytes);
+            v1 = load_chunk(a.seq, off + 16, a.n_bytes);
+        }
+    };
+    auto flush_out = [&](int n) {  // append the first n (<= 32) queued outputs to the emit buffer
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(a.cursor, (unsigned long long)n);
+        base = __shfl_sync(FULL, base, 0);
+        if (lane < n && base + lane < a.emit_cap) a.emit[base + lane] = out_q[lane];
+    };
+    auto drain = [&](int n) {  // exact path for the last n (<= 32) queued candidates
+        uint32_t dr[G];
+        uint32_t ok = 0, p0 = 0;
+        if (lane < n) {
+            p0 = cand_q[n_cand + lane];
+            ok = exact_group<G>(a, p0, dr);
+        }
+#pragma unroll
+        for (int j = 0; j < G; j++) {
+            const uint32_t m = __ballot_sync(FULL, (ok >> j) & 1u);
+            if (m == 0) continue;
+            if ((ok >> j) & 1u) out_q[n_out + __popc(m & lt)] = ((unsigned long long)(p0 + j) << 32) | dr[j];
+            n_out += __popc(m);
+            __syncwarp();
+            if (n_out >= 32) {
+                flush_out(32);
+                __syncwarp();
+                n_out -= 32;
+                if (lane < n_out) out_q[lane] = out_q[32 + lane];
+                __syncwarp();
+            }
+        }
+    };
+
+    uint4 cur0, cur1;
+    load_tile(tile, cur0, cur1);
 
     while (true) {
-        const uint64_t next_tile = tile + warps_total;
-        const long long cn = ((long long)next_tile * kTileLanes + lane - 1) * 2;
+        const uint32_t next_tile = tile + tile_stride;
         uint4 nxt0 = make_uint4(0, 0, 0, 0), nxt1 = nxt0;
-        if (next_tile < a.n_tiles) {
-            nxt0 = load_chunk(a.seq, cn, a.n_bytes);
-            nxt1 = load_chunk(a.seq, cn + 1, a.n_bytes);
-        }
+        if (next_tile < a.n_tiles) load_tile(next_tile, nxt0, nxt1);
 
         // ---- 32 bases -> 2 x 32 bits, previous lane's words as context ----
         const uint32_t A0 = pack16_filter(cur0), A1 = pack16_filter(cur1);
@@ -264,32 +316,66 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         if (lane == 0) hit = 0;  // halo lane: its positions belong to lane 31 of the previous tile
 
         // ---- queue the groups that passed; drain 32 at a time through the exact path ----
-        const uint64_t lane_pos = (uint64_t)c * 16;
-        while (true) {
-            const uint32_t any = __ballot_sync(FULL, hit != 0);
-            if (any == 0) break;
+        const uint32_t lane_pos = tile * kTileBytes + (uint32_t)lane_off;
+        uint32_t any = __ballot_sync(FULL, hit != 0);
+        while (any) {
             if (hit) {
                 const int t = __ffs(hit) - 1;
                 hit &= hit - 1;
-                queue[qcount + __popc(any & lt)] = lane_pos + (uint64_t)(G * t);
+                cand_q[n_cand + __popc(any & lt)] = lane_pos + (uint32_t)(G * t);
             }
-            qcount += __popc(any);
+            n_cand += __popc(any);
             __syncwarp();
-            if (qcount >= 32) {
-                qcount -= 32;
-                const uint64_t p0 = queue[qcount + lane];
-                exact_group<G>(a, p0);
+            if (n_cand >= 32) {
+                n_cand -= 32;
+                drain(32);
                 __syncwarp();
             }
+            any = __ballot_sync(FULL, hit != 0);
         }
 
         if (next_tile >= a.n_tiles) break;
         tile = next_tile;
-        c = cn;
         cur0 = nxt0;
         cur1 = nxt1;
     }
-    if (lane < qcount) exact_group<G>(a, queue[lane]);
+    if (n_cand) {
+        const int n = n_cand;
+        n_cand = 0;
+        drain(n);
+        __syncwarp();
+    }
+    if (n_out) flush_out(n_out);
+}
+
+// (position << 32 | hash) -> (genome << 32 | hash) for the entries one scan launch appended: emit[*done .. *cursor)
+struct ResolveArgs {
+    unsigned long long *emit;
+    const unsigned long long *cursor;  // cursor[0] = appended so far, cursor[1] = resolved so far
+    uint64_t emit_cap;
+    const uint64_t *seg_off;
+    const uint32_t *seg_genome;
+    uint32_t n_seg;
+    uint64_t pos_base;  // position of the launch's byte 0 in the coordinates of seg_off
+};
+__global__ void __launch_bounds__(256) kssd_resolve_kernel(const ResolveArgs a) {
+    unsigned long long end = a.cursor[0];
+    if (end > a.emit_cap) end = a.emit_cap;
+    for (unsigned long long i = a.cursor[1] + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < end;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long e = a.emit[i];
+        const uint64_t gpos = (e >> 32) + a.pos_base;
+        uint32_t lo = 0, hi = a.n_seg;  // owning segment: largest s with seg_off[s] <= pos
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (a.seg_off[mid] <= gpos) lo = mid; else hi = mid;
+        }
+        a.emit[i] = ((unsigned long long)a.seg_genome[lo] << 32) | (e & 0xFFFFFFFFull);
+    }
+}
+__global__ void kssd_commit_kernel(unsigned long long *cursor, uint64_t emit_cap) {
+    unsigned long long c = cursor[0];
+    cursor[1] = c < emit_cap ? c : emit_cap;
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------
@@ -319,19 +405,19 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
             vals.push_back((uint32_t)v);
         }
     }
-    // exact table, open addressing
+    // exact table: open addressing at load <= 1/16, so that the first probe of a non-retained dim_id almost
+    // always lands on an empty slot (one 64-bit load decides)
     uint64_t cap = 1024;
-    while (cap < 2 * keys.size()) cap <<= 1;
+    while (cap < 16 * keys.size()) cap <<= 1;
     int lg = 0;
     while ((1ull << lg) < cap) lg++;
     sp.table_mask = (uint32_t)(cap - 1);
     sp.table_shift = 32 - lg;
-    std::vector<uint32_t> tk(cap, 0xFFFFFFFFu), tv(cap, 0);
+    std::vector<unsigned long long> tab(cap, ~0ull);
     for (size_t i = 0; i < keys.size(); i++) {
         uint32_t slot = (keys[i] * 0x9E3779B1u) >> sp.table_shift;
-        while (tk[slot] != 0xFFFFFFFFu) slot = (slot + 1) & sp.table_mask;
-        tk[slot] = keys[i];
-        tv[slot] = vals[i];
+        while (tab[slot] != ~0ull) slot = (slot + 1) & sp.table_mask;
+        tab[slot] = ((unsigned long long)keys[i] << 32) | vals[i];
     }
     // bitmap: for every retained 2s-mer M and its reverse complement, and every alignment g < G of M against
     // the common span, one bit.  Index base i (i < nb) = base i + G-1-g of M, in the filter encoding
@@ -346,7 +432,7 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
             for (int g = 0; g < sp.group; g++) {
                 uint32_t idx = 0;
                 for (int b = 0; b < sp.nb; b++) {
-                    const int mo = b + sp.group - 1 - g;                       // base offset inside M (0 = first base)
+                    const int mo = b + sp.group - 1 - g;                                   // base offset inside M (0 = first base)
                     const uint32_t code = (uint32_t)(both[o] >> (2 * (m - 1 - mo))) & 3u;  // reference encoding
                     idx |= (code ^ (code >> 1)) << (2 * b);
                 }
@@ -356,11 +442,9 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
     }
     cudaStream_t st = c->stream;
     KSSD_TRY(c->d_bitmap.reserve(n_words * 4, st));
-    KSSD_TRY(c->d_tab_keys.reserve(cap * 4, st));
-    KSSD_TRY(c->d_tab_vals.reserve(cap * 4, st));
+    KSSD_TRY(c->d_tab_keys.reserve(cap * 8, st));
     KSSD_CUDA(cudaMemcpyAsync(c->d_bitmap.p, bm.data(), n_words * 4, cudaMemcpyHostToDevice, st));
-    KSSD_CUDA(cudaMemcpyAsync(c->d_tab_keys.p, tk.data(), cap * 4, cudaMemcpyHostToDevice, st));
-    KSSD_CUDA(cudaMemcpyAsync(c->d_tab_vals.p, tv.data(), cap * 4, cudaMemcpyHostToDevice, st));
+    KSSD_CUDA(cudaMemcpyAsync(c->d_tab_keys.p, tab.data(), cap * 8, cudaMemcpyHostToDevice, st));
     KSSD_CUDA(cudaStreamSynchronize(st));
     return KSSD_OK;
 }
@@ -372,8 +456,7 @@ static int launch_one(kssd_ctx *c, const ScanArgs &a, size_t smem) {
         KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done = true;
     }
-    uint64_t warps_per_cta = kScanThreads / 32;
-    uint64_t ctas = std::min<uint64_t>((a.n_tiles + warps_per_cta - 1) / warps_per_cta, (uint64_t)c->sm_count);
+    uint64_t ctas = std::min<uint64_t>(((uint64_t)a.n_tiles + kScanWarps - 1) / kScanWarps, (uint64_t)c->sm_count);
     if (ctas == 0) return KSSD_OK;
     if (c->profiling) KSSD_TRY(c->t_scan.begin(c->stream));
     kssd_scan_kernel<G, W0><<<(unsigned)ctas, kScanThreads, smem, c->stream>>>(a);
@@ -403,45 +486,65 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         set_error("2*half_k + group - 1 = %d bytes exceeds the exact path's %d-byte window", sp.kmer_size + sp.group - 1, 4 * kWindowWords);
         return KSSD_E_UNSUPPORTED;
     }
-    ScanArgs a;
-    a.seq = d_seq;
-    a.n_bytes = n_bytes;
-    a.seg_off = d_seg_off;
-    a.seg_genome = d_seg_genome;
-    a.n_seg = n_seg;
-    a.first_emit = first_emit;
-    a.pos_base = pos_base;
-    a.bitmap = c->d_bitmap.as<uint32_t>();
-    a.tab_keys = c->d_tab_keys.as<uint32_t>();
-    a.tab_vals = c->d_tab_vals.as<uint32_t>();
-    a.emit = c->d_emit.as<unsigned long long>();
-    a.cursor = c->d_cursor.as<unsigned long long>();
-    a.emit_cap = c->emit_cap;
-    a.sp = sp;
-    const uint64_t n_lane_chunks = (n_bytes + kLaneBases - 1) / kLaneBases;
-    a.n_tiles = (n_lane_chunks + kTileLanes - 1) / kTileLanes;
-    a.bitmap_words = (uint32_t)std::max<uint64_t>((1ull << (2 * sp.nb)) / 32, 4);
-    a.addr_mask = ((1u << sp.wbits) - 1) << 2;
     // test t of a lane covers k-mer ends G*t .. G*t+G-1 (lane-local); the bases common to their 2s-mer windows
     // start D = half_k + half_subk - G bases before base G*t.  [P0,P1,A0,A1] starts 32 bases before the lane.
     const int D = sp.half_k + sp.half_subk - sp.group;
     const int bit0 = 64 - 2 * D;
     if (bit0 < 0) { set_error("half_k + half_subk = %d too large for the 32-base context", sp.half_k + sp.half_subk); return KSSD_E_UNSUPPORTED; }
-    a.preshift = bit0 & 31;
-    const int w0 = bit0 >> 5;
-    size_t smem = (size_t)a.bitmap_words * 4 + (size_t)(kScanThreads / 32) * kQueueCap * sizeof(unsigned long long);
     // quality filter modes: compare is on a signed char (sketch.cpp:280)
-    bool use_qual = d_qual != nullptr && c->has_qual && c->least_qual > -128;
+    const bool use_qual = d_qual != nullptr && c->has_qual && c->least_qual > -128;
     if (use_qual && c->least_qual > 127) return KSSD_OK;  // no base can pass: nothing is emitted
-    a.qual = use_qual ? d_qual : nullptr;
+
+    ScanArgs a;
+    a.bitmap = c->d_bitmap.as<uint32_t>();
+    a.table = c->d_tab_keys.as<unsigned long long>();
+    a.emit = c->d_emit.as<unsigned long long>();
+    a.cursor = c->d_cursor.as<unsigned long long>();
+    a.emit_cap = c->emit_cap;
+    a.sp = sp;
+    a.bitmap_words = (uint32_t)std::max<uint64_t>((1ull << (2 * sp.nb)) / 32, 4);
+    a.addr_mask = ((1u << sp.wbits) - 1) << 2;
+    a.preshift = bit0 & 31;
     a.least_qual = c->least_qual;
-    switch (sp.group) {
-    case 1: return launch_w0<1>(c, a, smem, w0);
-    case 2: return launch_w0<2>(c, a, smem, w0);
-    case 3: return launch_w0<3>(c, a, smem, w0);
-    case 4: return launch_w0<4>(c, a, smem, w0);
-    default: set_error("bad filter group %d", sp.group); return KSSD_E_ARG;
+    const int w0 = bit0 >> 5;
+    const size_t smem = (size_t)a.bitmap_words * 4 + (size_t)kScanWarps * kQueueCap * (sizeof(uint32_t) + sizeof(unsigned long long));
+
+    // positions inside a launch are 32-bit: cut the buffer into pieces; a piece re-reads `halo` bytes of context
+    const uint64_t halo = 32;  // >= 2*half_k - 1, multiple of 16
+    for (uint64_t b0 = 0; b0 < n_bytes; b0 += kMaxPiece) {
+        const uint64_t b1 = std::min<uint64_t>(n_bytes, b0 + kMaxPiece);
+        const uint64_t from = b0 ? b0 - halo : 0;
+        a.seq = d_seq + from;
+        a.qual = use_qual ? d_qual + from : nullptr;
+        a.n_bytes = (uint32_t)(b1 - from);
+        // k-mers ending inside the halo belong to the previous piece; the caller's first_emit applies to byte 0
+        a.first_emit = (uint32_t)(b0 ? std::max<uint64_t>(halo, first_emit > from ? first_emit - from : 0)
+                                     : std::min<uint64_t>(first_emit, 0xFFFFFFFFull));
+        a.n_tiles = (a.n_bytes + kTileBytes - 1) / kTileBytes;
+        a.n_interior = a.n_bytes / kTileBytes;
+        int rc;
+        switch (sp.group) {
+        case 1: rc = launch_w0<1>(c, a, smem, w0); break;
+        case 2: rc = launch_w0<2>(c, a, smem, w0); break;
+        case 3: rc = launch_w0<3>(c, a, smem, w0); break;
+        case 4: rc = launch_w0<4>(c, a, smem, w0); break;
+        default: set_error("bad filter group %d", sp.group); return KSSD_E_ARG;
+        }
+        KSSD_TRY(rc);
+        ResolveArgs ra;
+        ra.emit = a.emit;
+        ra.cursor = a.cursor;
+        ra.emit_cap = a.emit_cap;
+        ra.seg_off = d_seg_off;
+        ra.seg_genome = d_seg_genome;
+        ra.n_seg = n_seg;
+        ra.pos_base = pos_base + from;
+        kssd_resolve_kernel<<<c->sm_count * 2, 256, 0, c->stream>>>(ra);
+        kssd_commit_kernel<<<1, 1, 0, c->stream>>>(a.cursor, a.emit_cap);
+        KSSD_CUDA(cudaGetLastError());
+        c->launches += 2;
     }
+    return KSSD_OK;
 }
 
 }  // namespace kssd
