@@ -32,7 +32,7 @@ struct ScanArgs {
     const uint8_t *qual;
     uint32_t n_bytes;          // <= 2^31: launch_scan cuts larger buffers into pieces
     uint32_t first_emit;       // k-mers ending before this byte are context only
-    const uint32_t *bitmap;    // membership bitmap (copied to shared memory)
+    const uint32_t *bitmap;    // membership bitmap followed by the second-level filter (copied to shared memory)
     const unsigned long long *table;  // exact retained-subset table: (dim_id << 32 | value), ~0 = empty
     unsigned long long *emit;  // (position << 32 | hash); resolve_kernel turns positions into genome ids
     unsigned long long *cursor;
@@ -54,6 +54,8 @@ static constexpr int kTileBytes = kTileLanes * kLaneBases;     // 992
 static constexpr int kQueueCap = 64;                           // per-warp candidate / output queue entries
 static constexpr int kWindowWords = 7;                         // 28 bytes >= 2k + G - 1 (k <= 12, G <= 4)
 static constexpr uint32_t kMaxPiece = 1u << 30;                // bytes per launch (positions are 32-bit)
+static constexpr int kL2Bits = 18;                             // second-level filter: 2^18 bits = 32 KB of shared memory
+static constexpr int kL2Words = (1 << kL2Bits) / 32;
 
 // ---- SWAR decode -----------------------------------------------------------------------------------------
 // filter encoding: bits 1-2 of the ASCII byte (A/a 0, C/c 1, T/t 2, G/g 3); 4 bytes -> 8 bits in the top byte,
@@ -128,26 +130,29 @@ __device__ __forceinline__ void load_window(const uint8_t *base, int start, uint
     for (int i = 0; i < kWindowWords; i++) w[i] = __funnelshift_r(U[i], U[i + 1], r8);
 }
 
-// complement-reverse of the 28 bases in c (first base most significant, 56 bits): base i lands at bits [2i, 2i+2)
-__device__ __forceinline__ uint64_t revcomp56(uint64_t c) {
-    uint64_t r = __brevll(c << 8);
-    r = ((r >> 1) & 0x5555555555555555ull) | ((r & 0x5555555555555555ull) << 1);
-    return ~r & 0x00FFFFFFFFFFFFFFull;
+// reverse the order of the 32 two-bit fields of x
+__device__ __forceinline__ uint64_t pairrev64(uint64_t x) {
+    uint64_t r = __brevll(x);
+    return ((r >> 1) & 0x5555555555555555ull) | ((r & 0x5555555555555555ull) << 1);
 }
 
-// Exact path for one queued group: k-mer end positions p0 .. p0+cnt-1.  Returns in ok a bit per position whose
-// k-mer is retained (all reference conditions checked), hashes in dr[].
-template <int G>
-__device__ __forceinline__ uint32_t exact_group(const ScanArgs &a, uint32_t p0, uint32_t (&dr)[G]) {
+// reference arithmetic from the two packings of a k-mer (sketch.cpp:496-524):
+//   tuple = bases first-most-significant, rvs = reverse complement; canonical min, dim_id of the inner 2s-mer
+__device__ __forceinline__ void canonical_dim(const ScanParams &sp, uint64_t tuple, uint64_t rvs, uint64_t &uni, uint32_t &dim) {
+    uni = tuple < rvs ? tuple : rvs;
+    dim = (uint32_t)((uni & sp.domask) >> (2 * sp.hoc));
+}
+
+// Stage 2 (exact): one k-mer END position p per lane, everything re-derived from the raw bytes with the
+// reference's semantics.  Returns true and the hash when the k-mer is retained.
+__device__ __forceinline__ bool verify_kmer(const ScanArgs &a, uint32_t p, uint32_t &hash) {
     const ScanParams &sp = a.sp;
     const int L = sp.kmer_size;
-    int cnt = kLaneBases - (int)(p0 % kLaneBases);
-    if (cnt > G) cnt = G;
-    const int start = (int)p0 - (L - 1);
+    const int start = (int)p - (L - 1);
     uint32_t w[kWindowWords];
     load_window(a.seq, start, a.n_bytes, w);
-    uint64_t C = 0;   // 2-bit codes of the 28 bytes, first byte most significant
-    uint32_t E = 0;   // non-zero <=> some byte of the window is not a base
+    uint64_t C = 0;  // 2-bit codes of the 28 bytes, first byte most significant
+    uint32_t E = 0;  // non-zero <=> some byte of the 28 is not a base
     uint32_t err[kWindowWords];
 #pragma unroll
     for (int i = 0; i < kWindowWords; i++) {
@@ -156,66 +161,87 @@ __device__ __forceinline__ uint32_t exact_group(const ScanArgs &a, uint32_t p0, 
         C = (C << 8) | pack4_msb(code);
         E |= err[i];
     }
-    const uint64_t R = revcomp56(C);
-    // probe the exact table for every position of the group; loads are independent
-    unsigned long long kv[G];
-    uint64_t uni[G];
-    uint32_t dim[G], slot[G];
+    const uint64_t tuple = (C >> (2 * (4 * kWindowWords - L))) & sp.tupmask;
+    const uint64_t rvs = (~pairrev64(tuple) >> (64 - 2 * L)) & sp.tupmask;
+    uint64_t uni;
+    uint32_t dim;
+    canonical_dim(sp, tuple, rvs, uni, dim);
+    uint32_t s = (dim * 0x9E3779B1u) >> sp.table_shift;
+    unsigned long long e = __ldg(a.table + s);
+    while (e != ~0ull && (uint32_t)(e >> 32) != dim) {
+        s = (s + 1) & sp.table_mask;
+        e = __ldg(a.table + s);
+    }
+    if (e == ~0ull) return false;  // not in the retained subset (sketch.cpp:509-511)
+    const uint32_t lmask = (1u << L) - 1u;  // L <= 24
+    if (E) {  // exact per-byte validity (sketch.cpp:494-505): every base of the window must be ACGTacgt
+        uint32_t V = 0;
+#pragma unroll
+        for (int i = 0; i < kWindowWords; i++) V |= (~nz4(err[i]) & 0xFu) << (4 * i);
+        if ((V & lmask) != lmask) return false;
+    }
+    if (p < a.first_emit) return false;  // context of a continued record
+    if (a.qual) {  // valid only if (signed char)quality >= least_qual (sketch.cpp:280)
+        uint32_t qw[kWindowWords];
+        load_window(a.qual, start, a.n_bytes, qw);
+        const uint32_t lq4 = (uint32_t)(a.least_qual & 0xFF) * 0x01010101u;
+        uint32_t QV = 0;
+#pragma unroll
+        for (int i = 0; i < kWindowWords; i++) QV |= nz4(__vcmpges4(qw[i], lq4)) << (4 * i);
+        if ((QV & lmask) != lmask) return false;
+    }
+    hash = (uint32_t)((((uni & sp.undomask0) | ((uni & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | (uint32_t)e);
+    return true;
+}
+
+// Stage 1 (still approximate, no memory traffic): one queued group per lane.  The group's bases come from the
+// packed words saved at enqueue time ([P0,P1,A0,A1], filter encoding, garbage for non-bases); for each of its
+// positions the canonical dim_id is looked up in the second-level shared-memory filter.  Returns a bit per
+// position that still may be retained.
+template <int G>
+__device__ __forceinline__ uint32_t screen_group(const ScanArgs &a, const uint32_t *s_l2, uint32_t pos, uint4 sw) {
+    const ScanParams &sp = a.sp;
+    const int L = sp.kmer_size;
+    const int e0 = (int)(pos % kLaneBases);
+    int cnt = kLaneBases - e0;
+    if (cnt > G) cnt = G;
+    // 64 bits of [P0,P1,A0,A1,0,0] starting at the first base of the group's first k-mer
+    const int b = 66 - 2 * L + 2 * e0;  // lane-local base i sits at bit 64 + 2i
+    const bool w2 = b & 64, w1 = b & 32;
+    const int sh = b & 31;
+    const uint32_t t0 = w2 ? sw.z : sw.x, t1 = w2 ? sw.w : sw.y, t2 = w2 ? 0u : sw.z, t3 = w2 ? 0u : sw.w;
+    const uint32_t x0 = w1 ? t1 : t0, x1 = w1 ? t2 : t1, x2 = w1 ? t3 : t2;
+    uint32_t flo = __funnelshift_r(x0, x1, sh), fhi = __funnelshift_r(x1, x2, sh);
+    // filter encoding (A0 C1 T2 G3) -> reference encoding (A0 C1 G2 T3)
+    flo ^= (flo >> 1) & 0x55555555u;
+    fhi ^= (fhi >> 1) & 0x55555555u;
+    const uint64_t F = ((uint64_t)fhi << 32) | flo;  // base q of the window at bits [2q, 2q+2)
+    const uint64_t Fr = pairrev64(F);                // base q at bits [62-2q, 64-2q)
+    uint32_t pass = 0;
 #pragma unroll
     for (int j = 0; j < G; j++) {
-        const uint64_t tuple = (C >> (2 * (4 * kWindowWords - L - j))) & sp.tupmask;
-        const uint64_t rvs = (R >> (2 * j)) & sp.tupmask;
-        uni[j] = tuple < rvs ? tuple : rvs;
-        dim[j] = (uint32_t)((uni[j] & sp.domask) >> (2 * sp.hoc));
-        slot[j] = (dim[j] * 0x9E3779B1u) >> sp.table_shift;
-        kv[j] = __ldg(a.table + slot[j]);
+        const uint64_t tuple = (Fr >> (64 - 2 * (j + L))) & sp.tupmask;
+        const uint64_t rvs = (~F >> (2 * j)) & sp.tupmask;
+        uint64_t uni;
+        uint32_t dim;
+        canonical_dim(sp, tuple, rvs, uni, dim);
+        const uint32_t h = (dim * 0x9E3779B1u) >> (32 - kL2Bits);
+        const uint32_t word = s_l2[h >> 5];
+        if (j < cnt && ((word >> (h & 31)) & 1u)) pass |= 1u << j;
     }
-    uint32_t ok = 0;
-#pragma unroll
-    for (int j = 0; j < G; j++) {
-        dr[j] = 0;
-        if (kv[j] == ~0ull || j >= cnt) continue;  // empty slot: not retained (the common case)
-        // rare from here on: a retained dim_id or a hash collision
-        unsigned long long e = kv[j];
-        uint32_t s = slot[j];
-        while (e != ~0ull && (uint32_t)(e >> 32) != dim[j]) {
-            s = (s + 1) & sp.table_mask;
-            e = __ldg(a.table + s);
-        }
-        if (e == ~0ull) continue;
-        const uint32_t lmask = (1u << L) - 1u;  // L <= 24
-        if (E) {  // exact per-byte validity (sketch.cpp:494-505): every base of the window must be ACGTacgt
-            uint32_t V = 0;
-#pragma unroll
-            for (int i = 0; i < kWindowWords; i++) V |= (~nz4(err[i]) & 0xFu) << (4 * i);
-            if (((V >> j) & lmask) != lmask) continue;
-        }
-        if (p0 + j < a.first_emit) continue;  // context of a continued record
-        if (a.qual) {  // valid only if (signed char)quality >= least_qual (sketch.cpp:280); survivors only
-            uint32_t qw[kWindowWords];
-            load_window(a.qual, start, a.n_bytes, qw);
-            const uint32_t lq4 = (uint32_t)(a.least_qual & 0xFF) * 0x01010101u;
-            uint32_t QV = 0;
-#pragma unroll
-            for (int i = 0; i < kWindowWords; i++) QV |= nz4(__vcmpges4(qw[i], lq4)) << (4 * i);
-            if (((QV >> j) & lmask) != lmask) continue;
-        }
-        const uint64_t u = uni[j];
-        dr[j] = (uint32_t)((((u & sp.undomask0) | ((u & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | (uint32_t)e);
-        ok |= 1u << j;
-    }
-    return ok;
+    return pass;
 }
 
 // G: k-mer end positions decided per bitmap test.  W0: word offset (0/1) of the first index base of test 0.
 template <int G, int W0>
 __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid_constant__ ScanArgs a) {
-    extern __shared__ uint32_t s_mem[];
+    extern __shared__ uint4 s_mem4[];
+    uint32_t *s_mem = reinterpret_cast<uint32_t *>(s_mem4);
     uint32_t *s_bitmap = s_mem;
+    uint32_t *s_l2 = s_mem + a.bitmap_words;
     {
-        const uint4 *src = reinterpret_cast<const uint4 *>(a.bitmap);
-        uint4 *dst = reinterpret_cast<uint4 *>(s_bitmap);
-        for (uint32_t i = threadIdx.x; i < a.bitmap_words / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+        const uint4 *src = reinterpret_cast<const uint4 *>(a.bitmap);  // bitmap followed by the second-level filter
+        for (uint32_t i = threadIdx.x; i < (a.bitmap_words + kL2Words) / 4; i += blockDim.x) s_mem4[i] = __ldg(src + i);
     }
     __syncthreads();
 
@@ -223,8 +249,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     constexpr int T = (kLaneBases + G - 1) / G;  // tests per lane
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    uint32_t *cand_q = s_mem + a.bitmap_words + warp * kQueueCap;                                        // positions
-    unsigned long long *out_q = reinterpret_cast<unsigned long long *>(s_mem + a.bitmap_words + kScanWarps * kQueueCap) + warp * kQueueCap;
+    uint4 *cand_s = s_mem4 + (a.bitmap_words + kL2Words) / 4 + warp * kQueueCap;                      // [P0,P1,A0,A1] per candidate
+    uint32_t *cand_pos = s_mem + a.bitmap_words + kL2Words + kScanWarps * kQueueCap * 4 + warp * kQueueCap;
+    uint32_t *ver_pos = cand_pos + kScanWarps * kQueueCap;
     const uint32_t tile_stride = gridDim.x * kScanWarps;
     // interleave warps of different CTAs over consecutive tiles so that all SMs stream the same HBM region
     uint32_t tile = (uint32_t)warp * gridDim.x + blockIdx.x;
@@ -232,10 +259,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     const uint32_t addr_mask = a.addr_mask;
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
-    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t lt;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
     const int lane_off = (lane - 1) * kLaneBases;
     const uint8_t *lane_ptr = a.seq + lane_off;  // lane 0: before the tile (halo)
-    int n_cand = 0, n_out = 0;
+    int n_cand = 0, n_ver = 0;
 
     auto load_tile = [&](uint32_t tl, uint4 &v0, uint4 &v1) {
         if (tl >= 1 && tl < a.n_interior) {
@@ -248,31 +276,37 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             v1 = load_chunk(a.seq, off + 16, a.n_bytes);
         }
     };
-    auto flush_out = [&](int n) {  // append the first n (<= 32) queued outputs to the emit buffer
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(a.cursor, (unsigned long long)n);
-        base = __shfl_sync(FULL, base, 0);
-        if (lane < n && base + lane < a.emit_cap) a.emit[base + lane] = out_q[lane];
-    };
-    auto drain = [&](int n) {  // exact path for the last n (<= 32) queued candidates
-        uint32_t dr[G];
-        uint32_t ok = 0, p0 = 0;
+    auto stage2 = [&](int base, int n) {  // exact path for queued positions [base, base+n), append survivors to the emit buffer
+        uint32_t p = 0, hash = 0;
+        bool ok = false;
         if (lane < n) {
-            p0 = cand_q[n_cand + lane];
-            ok = exact_group<G>(a, p0, dr);
+            p = ver_pos[base + lane];
+            ok = verify_kmer(a, p, hash);
+        }
+        const uint32_t m = __ballot_sync(FULL, ok);
+        if (m) {
+            unsigned long long at = 0;
+            if (lane == 0) at = atomicAdd(a.cursor, (unsigned long long)__popc(m));
+            at = __shfl_sync(FULL, at, 0) + __popc(m & lt);
+            if (ok && at < a.emit_cap) a.emit[at] = ((unsigned long long)p << 32) | hash;
+        }
+    };
+    auto stage1 = [&](int base, int n) {  // screen queued groups [base, base+n), queue surviving positions for stage 2
+        uint32_t pos = 0, pass = 0;
+        if (lane < n) {
+            pos = cand_pos[base + lane];
+            pass = screen_group<G>(a, s_l2, pos, cand_s[base + lane]);
         }
 #pragma unroll
         for (int j = 0; j < G; j++) {
-            const uint32_t m = __ballot_sync(FULL, (ok >> j) & 1u);
+            const uint32_t m = __ballot_sync(FULL, (pass >> j) & 1u);
             if (m == 0) continue;
-            if ((ok >> j) & 1u) out_q[n_out + __popc(m & lt)] = ((unsigned long long)(p0 + j) << 32) | dr[j];
-            n_out += __popc(m);
+            if ((pass >> j) & 1u) ver_pos[n_ver + __popc(m & lt)] = pos + j;
+            n_ver += __popc(m);
             __syncwarp();
-            if (n_out >= 32) {
-                flush_out(32);
-                __syncwarp();
-                n_out -= 32;
-                if (lane < n_out) out_q[lane] = out_q[32 + lane];
+            if (n_ver >= 32) {
+                n_ver -= 32;
+                stage2(n_ver, 32);
                 __syncwarp();
             }
         }
@@ -315,23 +349,28 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         }
         if (lane == 0) hit = 0;  // halo lane: its positions belong to lane 31 of the previous tile
 
-        // ---- queue the groups that passed; drain 32 at a time through the exact path ----
-        const uint32_t lane_pos = tile * kTileBytes + (uint32_t)lane_off;
+        // ---- queue the groups that passed (ballot + popc, no atomics); screen 32 at a time ----
         uint32_t any = __ballot_sync(FULL, hit != 0);
-        while (any) {
-            if (hit) {
-                const int t = __ffs(hit) - 1;
-                hit &= hit - 1;
-                cand_q[n_cand + __popc(any & lt)] = lane_pos + (uint32_t)(G * t);
-            }
-            n_cand += __popc(any);
-            __syncwarp();
-            if (n_cand >= 32) {
-                n_cand -= 32;
-                drain(32);
+        if (any) {
+            const uint32_t lane_pos = tile * kTileBytes + (uint32_t)lane_off;
+            const uint4 sw = make_uint4(P0, P1, A0, A1);
+            do {
+                if (hit) {
+                    const int t = __ffs(hit) - 1;
+                    hit &= hit - 1;
+                    const int slot = n_cand + __popc(any & lt);
+                    cand_pos[slot] = lane_pos + (uint32_t)(G * t);
+                    cand_s[slot] = sw;
+                }
+                n_cand += __popc(any);
                 __syncwarp();
-            }
-            any = __ballot_sync(FULL, hit != 0);
+                if (n_cand >= 32) {
+                    n_cand -= 32;
+                    stage1(n_cand, 32);
+                    __syncwarp();
+                }
+                any = __ballot_sync(FULL, hit != 0);
+            } while (any);
         }
 
         if (next_tile >= a.n_tiles) break;
@@ -339,13 +378,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         cur0 = nxt0;
         cur1 = nxt1;
     }
-    if (n_cand) {
-        const int n = n_cand;
-        n_cand = 0;
-        drain(n);
-        __syncwarp();
-    }
-    if (n_out) flush_out(n_out);
+    if (n_cand) stage1(0, n_cand);
+    __syncwarp();
+    if (n_ver) stage2(0, n_ver);
 }
 
 // (position << 32 | hash) -> (genome << 32 | hash) for the entries one scan launch appended: emit[*done .. *cursor)
@@ -440,10 +475,16 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
             }
         }
     }
+    // second-level filter: one bit per retained (canonical) dim_id at a multiplicative hash of it
+    bm.resize(n_words + kL2Words, 0);
+    for (size_t i = 0; i < keys.size(); i++) {
+        const uint32_t h = (keys[i] * 0x9E3779B1u) >> (32 - kL2Bits);
+        bm[n_words + (h >> 5)] |= 1u << (h & 31);
+    }
     cudaStream_t st = c->stream;
-    KSSD_TRY(c->d_bitmap.reserve(n_words * 4, st));
+    KSSD_TRY(c->d_bitmap.reserve(bm.size() * 4, st));
     KSSD_TRY(c->d_tab_keys.reserve(cap * 8, st));
-    KSSD_CUDA(cudaMemcpyAsync(c->d_bitmap.p, bm.data(), n_words * 4, cudaMemcpyHostToDevice, st));
+    KSSD_CUDA(cudaMemcpyAsync(c->d_bitmap.p, bm.data(), bm.size() * 4, cudaMemcpyHostToDevice, st));
     KSSD_CUDA(cudaMemcpyAsync(c->d_tab_keys.p, tab.data(), cap * 8, cudaMemcpyHostToDevice, st));
     KSSD_CUDA(cudaStreamSynchronize(st));
     return KSSD_OK;
@@ -453,7 +494,7 @@ template <int G, int W0>
 static int launch_one(kssd_ctx *c, const ScanArgs &a, size_t smem) {
     static bool attr_done = false;  // one flag per template instantiation
     if (!attr_done) {
-        KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
         attr_done = true;
     }
     uint64_t ctas = std::min<uint64_t>(((uint64_t)a.n_tiles + kScanWarps - 1) / kScanWarps, (uint64_t)c->sm_count);
@@ -507,7 +548,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.preshift = bit0 & 31;
     a.least_qual = c->least_qual;
     const int w0 = bit0 >> 5;
-    const size_t smem = (size_t)a.bitmap_words * 4 + (size_t)kScanWarps * kQueueCap * (sizeof(uint32_t) + sizeof(unsigned long long));
+    const size_t smem = (size_t)(a.bitmap_words + kL2Words) * 4 + (size_t)kScanWarps * kQueueCap * (sizeof(uint4) + 2 * sizeof(uint32_t));
 
     // positions inside a launch are 32-bit: cut the buffer into pieces; a piece re-reads `halo` bytes of context
     const uint64_t halo = 32;  // >= 2*half_k - 1, multiple of 16
