@@ -43,6 +43,7 @@ struct ScanArgs {
     uint32_t addr_mask;        // ((1<<wbits)-1) << 2
     int preshift;              // bit offset (mod 32) of the first index base of test 0 inside [P0,P1,A0,A1]
     int least_qual;
+    int aligned32;             // seq is 32-byte aligned: tiles are read with 256-bit loads
     ScanParams sp;
 };
 
@@ -87,6 +88,18 @@ __device__ __forceinline__ uint32_t pack4_msb(uint32_t code) { return (code * 0x
 __device__ __forceinline__ uint32_t nz4(uint32_t e) {
     uint32_t f = (((e & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e) & 0x80808080u;
     return ((f >> 7) * 0x01020408u) >> 24 & 0xFu;
+}
+
+// one 256-bit global load (sm_100: LDG.E.256): a warp reads 1 KB contiguous with ONE instruction, so every
+// 32-byte sector is requested once (two 128-bit loads per lane would touch each sector twice)
+__device__ __forceinline__ void ldg256(const uint8_t *p, uint4 &v0, uint4 &v1) {
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v0.x), "=r"(v0.y), "=r"(v0.z), "=r"(v0.w), "=r"(v1.x), "=r"(v1.y), "=r"(v1.z), "=r"(v1.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 // 16 bytes at byte offset off (multiple of 16, may be negative); bytes outside [0, n_bytes) read as 0x00
@@ -264,12 +277,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     const int lane_off = (lane - 1) * kLaneBases;
     const uint8_t *lane_ptr = a.seq + lane_off;  // lane 0: before the tile (halo)
     int n_cand = 0, n_ver = 0;
+    // 32-bit shared-window addresses of this warp's queues (kept in registers; the enqueue round is hot)
+    uint32_t cand_pos_sa = (uint32_t)__cvta_generic_to_shared(cand_pos);
+    uint32_t cand_s_sa = (uint32_t)__cvta_generic_to_shared(cand_s);
+    uint32_t lane_off_u = (uint32_t)lane_off;
+    // opaque to the optimiser: otherwise it re-derives these from threadIdx / kernel parameters in every round
+    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off_u), "+l"(lane_ptr));
 
     auto load_tile = [&](uint32_t tl, uint4 &v0, uint4 &v1) {
         if (tl >= 1 && tl < a.n_interior) {
-            const uint4 *p = reinterpret_cast<const uint4 *>(lane_ptr + (size_t)tl * kTileBytes);
-            v0 = __ldg(p);
-            v1 = __ldg(p + 1);
+            const uint8_t *p = lane_ptr + (size_t)tl * kTileBytes;
+            if (a.aligned32) {
+                ldg256(p, v0, v1);
+            } else {
+                v0 = __ldg(reinterpret_cast<const uint4 *>(p));
+                v1 = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
+            }
         } else {
             const int off = (int)(tl * kTileBytes) + lane_off;
             v0 = load_chunk(a.seq, off, a.n_bytes);
@@ -352,15 +375,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         // ---- queue the groups that passed (ballot + popc, no atomics); screen 32 at a time ----
         uint32_t any = __ballot_sync(FULL, hit != 0);
         if (any) {
-            const uint32_t lane_pos = tile * kTileBytes + (uint32_t)lane_off;
+            const uint32_t lane_pos = tile * kTileBytes + lane_off_u;
             const uint4 sw = make_uint4(P0, P1, A0, A1);
             do {
                 if (hit) {
                     const int t = __ffs(hit) - 1;
                     hit &= hit - 1;
-                    const int slot = n_cand + __popc(any & lt);
-                    cand_pos[slot] = lane_pos + (uint32_t)(G * t);
-                    cand_s[slot] = sw;
+                    const uint32_t slot = (uint32_t)n_cand + __popc(any & lt);
+                    sts32(cand_pos_sa + slot * 4, lane_pos + (uint32_t)(G * t));
+                    sts128(cand_s_sa + slot * 16, sw);
                 }
                 n_cand += __popc(any);
                 __syncwarp();
@@ -556,6 +579,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         const uint64_t b1 = std::min<uint64_t>(n_bytes, b0 + kMaxPiece);
         const uint64_t from = b0 ? b0 - halo : 0;
         a.seq = d_seq + from;
+        a.aligned32 = (reinterpret_cast<uintptr_t>(a.seq) & 31) == 0;
         a.qual = use_qual ? d_qual + from : nullptr;
         a.n_bytes = (uint32_t)(b1 - from);
         // k-mers ending inside the halo belong to the previous piece; the caller's first_emit applies to byte 0
