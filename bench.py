@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--family", type=int, default=10)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-genomes", type=int, default=32)
+    ap.add_argument("--cpu-sample-genomes", type=int, default=256)
     return ap.parse_args()
 
 

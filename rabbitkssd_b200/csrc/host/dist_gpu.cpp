@@ -1,0 +1,325 @@
+// Drop-in replacements for index_tridist / index_dist (RabbitKSSD src/dist.h:35-37, implemented in
+// src/dist.cpp:22-343, :429-776) on top of libkssd_b200.so.
+//
+// Same signatures and file side effects: <refSketchOut>.index/.dict are re-read from disk exactly as the reference
+// does (dist.cpp:83-130, :488-523), results go to per-"thread" sub-files <out>.dir/<out>.<t> (+ <out>.index.<t>)
+// which are concatenated under the header into <out> when they total <= 4 GiB and otherwise kept together with
+// <out>.index (dist.cpp:276-336, :710-770).  The posting accumulation and the O(rows x cols) epilogue run on the GPU;
+// the device returns (row, col, common) for every cell that passes a conservative threshold test and this file
+// recomputes Jaccard / containment and the distance with the reference's own double expressions and libm log()
+// (dist.cpp:216-232, :237-251, :608-624, :647-661), so the kept pair set and the printed %f values are identical.
+#include <omp.h>
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <queue>
+#include <vector>
+
+#include "dist.h"
+#include "kssd_host.h"
+
+namespace {
+
+using kssd_host::check;
+
+// .index / .dict of the 32-bit path, as written by transSketches (sketch.cpp:1006-1011)
+struct IndexFiles {
+    size_t hashSize = 0;
+    uint64_t totalIndex = 0;
+    std::vector<uint32_t> counts, dict;
+};
+
+void read_index(const std::string &indexFile, const std::string &dictFile, const char *who, IndexFiles &ix) {
+    FILE *fp = fopen(indexFile.c_str(), "rb");
+    if (!fp) {
+        std::cerr << "ERROR: " << who << ", cannot open the index sketch file: " << indexFile << std::endl;
+        exit(1);
+    }
+    const size_t r0 = fread(&ix.hashSize, sizeof(size_t), 1, fp);
+    const size_t r1 = fread(&ix.totalIndex, sizeof(uint64_t), 1, fp);
+    if (r0 != 1 || r1 != 1) {
+        std::cerr << "ERROR: " << who << ", error read hash_size, total_index" << std::endl;
+        exit(1);
+    }
+    ix.counts.resize(ix.hashSize);
+    const size_t r2 = fread(ix.counts.data(), sizeof(uint32_t), ix.hashSize, fp);
+    fclose(fp);
+    ix.dict.resize(ix.totalIndex);
+    FILE *fd = fopen(dictFile.c_str(), "rb");
+    if (!fd) {
+        std::cerr << "ERROR: " << who << ", cannot open the dictionary sketch file: " << dictFile << std::endl;
+        exit(1);
+    }
+    const size_t r3 = fread(ix.dict.data(), sizeof(uint32_t), ix.totalIndex, fd);
+    fclose(fd);
+    if (r2 != ix.hashSize || r3 != ix.totalIndex) {
+        std::cerr << "ERROR: " << who << ", error read hash_size, total_index, sketch_size_arr, index_arr" << std::endl;
+        exit(1);
+    }
+}
+
+void flatten(const std::vector<sketch_t> &sk, std::vector<uint32_t> &flat, std::vector<uint64_t> &off, std::vector<uint32_t> &sizes) {
+    off.assign(sk.size() + 1, 0);
+    sizes.resize(sk.size());
+    for (size_t i = 0; i < sk.size(); i++) {
+        sizes[i] = (uint32_t)sk[i].hashSet.size();
+        off[i + 1] = off[i] + sizes[i];
+    }
+    flat.resize(off.back());
+    for (size_t i = 0; i < sk.size(); i++)
+        if (sizes[i]) memcpy(flat.data() + off[i], sk[i].hashSet.data(), (size_t)sizes[i] * sizeof(uint32_t));
+}
+
+int collect_hits(void *user, const kssd_hit *hits, size_t n) {
+    std::vector<kssd_hit> *v = reinterpret_cast<std::vector<kssd_hit> *>(user);
+    v->insert(v->end(), hits, hits + n);
+    return 0;
+}
+
+// the reference's expressions, verbatim in meaning: dist.cpp:216-231 / :237-250
+inline void exact_distance(int common, int size0, int size1, int kmer_size, int isContainment, double &jorc, double &dist) {
+    if (!isContainment) {
+        const int denom = size0 + size1 - common;
+        jorc = (size0 == 0 || size1 == 0) ? 0.0 : (double)common / denom;
+        if (jorc == 1.0) dist = 0.0;
+        else if (jorc == 0.0) dist = 1.0;
+        else dist = (double)-1.0 / kmer_size * log((2 * jorc) / (1.0 + jorc));
+    } else {
+        const int denom = std::min(size0, size1);
+        jorc = (size0 == 0 || size1 == 0) ? 0.0 : (double)common / denom;
+        if (jorc == 1.0) dist = 0.0;
+        else if (jorc == 0.0) dist = 1.0;
+        else dist = (double)-1.0 / kmer_size * log(jorc);
+    }
+}
+
+// Sub-file policy shared by both entry points (dist.cpp:143-168, :276-336): rows are dealt to numThreads sub-files
+// (the reference's OpenMP dynamic schedule makes the assignment arbitrary; here row r goes to file r % numThreads).
+struct SubFiles {
+    std::string outputFile, folderPath;
+    std::vector<std::string> dist_file_list, dist_index_list;
+    std::vector<FILE *> fpArr, fpIndexArr;
+
+    SubFiles(const std::string &out, int numThreads) : outputFile(out), folderPath(out + ".dir") {
+        const std::string cmd = "mkdir -p " + folderPath;
+        if (!system(cmd.c_str())) std::cerr << "success create: " << folderPath << std::endl;
+        for (int i = 0; i < numThreads; i++) {
+            dist_file_list.push_back(folderPath + '/' + outputFile + '.' + std::to_string(i));
+            fpArr.push_back(fopen(dist_file_list.back().c_str(), "w+"));
+            dist_index_list.push_back(outputFile + ".index." + std::to_string(i));
+            fpIndexArr.push_back(fopen(dist_index_list.back().c_str(), "w+"));
+            if (!fpArr.back() || !fpIndexArr.back()) {
+                std::cerr << "ERROR: cannot open the distance sub-file: " << dist_file_list.back() << std::endl;
+                exit(1);
+            }
+        }
+    }
+
+    void finish() {
+        const int numThreads = (int)fpArr.size();
+        for (int i = 0; i < numThreads; i++) {
+            fclose(fpArr[i]);
+            fclose(fpIndexArr[i]);
+        }
+        uint64_t totalSize = 0;
+        const uint64_t maxSize = 1LLU << 32;  // max total distance file size 4GB
+        for (int i = 0; i < numThreads; i++) {
+            struct stat st;
+            st.st_size = 0;
+            stat(dist_file_list[i].c_str(), &st);
+            totalSize += st.st_size;
+        }
+        const int bufSize = 1 << 24;
+        std::vector<char> buf(bufSize + 1);
+        auto concat = [&](const std::string &from, FILE *to) {
+            FILE *f = fopen(from.c_str(), "rb+");
+            if (!f) return;
+            while (true) {
+                const size_t got = fread(buf.data(), 1, bufSize, f);
+                fwrite(buf.data(), 1, got, to);
+                if (got < (size_t)bufSize) break;
+            }
+            fclose(f);
+        };
+        if (totalSize <= maxSize) {
+            FILE *com = fopen(outputFile.c_str(), "w");
+            std::cerr << "-----save the output distance file: " << outputFile << std::endl;
+            fprintf(com, " genome0\tgenome1\tcommon|size0|size1\tjaccard\tmashD\n");
+            for (int i = 0; i < numThreads; i++) {
+                concat(dist_file_list[i], com);
+                remove(dist_file_list[i].c_str());
+                remove(dist_index_list[i].c_str());
+            }
+            remove(folderPath.c_str());
+            fclose(com);
+        } else {
+            std::cerr << "-----the output distance file is too big to merge into one single file, saving the result into directory: "
+                      << folderPath << std::endl;
+            const std::string outputIndexFile = outputFile + ".index";
+            std::cerr << "-----save the index between genomes and distance sub-files into: " << outputIndexFile << std::endl;
+            FILE *com = fopen(outputIndexFile.c_str(), "w+");
+            fprintf(com, "genomeName\tdistFileName\n");
+            for (int i = 0; i < numThreads; i++) {
+                concat(dist_index_list[i], com);
+                remove(dist_index_list[i].c_str());
+            }
+            fclose(com);
+        }
+    }
+};
+
+void refuse64(const sketchInfo_t &info, const char *who) {
+    if (info.half_k - info.drlevel > 8) {
+        fprintf(stderr, "ERROR: %s: the 64-bit hash path is not implemented in the B200 build\n", who);
+        exit(1);
+    }
+}
+
+// hits sorted by (row, col); row_begin[r] .. row_begin[r+1] index the hits of row r
+void group_by_row(std::vector<kssd_hit> &hits, size_t n_rows, std::vector<size_t> &row_begin) {
+    std::sort(hits.begin(), hits.end(), [](const kssd_hit &a, const kssd_hit &b) { return a.row != b.row ? a.row < b.row : a.col < b.col; });
+    row_begin.assign(n_rows + 1, 0);
+    for (const kssd_hit &h : hits) row_begin[h.row + 1]++;
+    for (size_t r = 0; r < n_rows; r++) row_begin[r + 1] += row_begin[r];
+}
+
+}  // namespace
+
+void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSketchOut, string outputFile, int kmer_size,
+                   double maxDist, int isContainment, int numThreads) {
+    const double t0 = get_sec();
+    refuse64(info, "index_tridist()");
+    std::cerr << "-----not use hash64 in index_tridist() " << std::endl;
+    IndexFiles ix;
+    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_tridist()", ix);
+    std::vector<uint32_t> flat, sizes;
+    std::vector<uint64_t> off;
+    flatten(sketches, flat, off, sizes);
+    kssd_ctx *ctx = kssd_host::context();
+    check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(), (uint32_t)sizes.size()),
+          "index_load");
+    const double t1 = get_sec();
+    std::cerr << "===================time of read index and offset sketch file is: " << t1 - t0 << std::endl;
+
+    const size_t numRef = sketches.size();
+    if (numThreads < 1) numThreads = 1;
+    SubFiles sub(outputFile, numThreads);
+    std::cerr << "=====total: " << numRef << std::endl;
+    std::vector<kssd_hit> hits;
+    check(kssd_b200_dist_rows(ctx, flat.data(), off.data(), (uint32_t)numRef, KSSD_PTR_HOST, 0, (uint32_t)numRef, 1, kmer_size, maxDist,
+                              isContainment, collect_hits, &hits),
+          "dist_rows");
+    std::vector<size_t> row_begin;
+    group_by_row(hits, numRef, row_begin);
+
+#pragma omp parallel for num_threads(numThreads) schedule(static, 1)
+    for (int t = 0; t < numThreads; t++) {
+        std::string strBuf;
+        for (size_t i = t; i < numRef; i += numThreads) {
+            fprintf(sub.fpIndexArr[t], "%s\t%s\n", sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
+            for (size_t k = row_begin[i]; k < row_begin[i + 1]; k++) {
+                const size_t j = hits[k].col;
+                const int common = (int)hits[k].common, size0 = (int)sizes[i], size1 = (int)sizes[j];
+                double jorc, d;
+                exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
+                if (d < maxDist)  // strict, dist.cpp:232 / :251
+                    strBuf += sketches[j].fileName + '\t' + sketches[i].fileName + '\t' + to_string(common) + '|' + to_string(size0) + '|' +
+                              to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
+            }
+            if (strBuf.size() > (1u << 22)) {
+                fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+                strBuf.clear();
+            }
+        }
+        fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+    }
+    const double t2 = get_sec();
+    std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
+    sub.finish();
+    std::cerr << "===================time of merge the subFiles into final files is: " << get_sec() - t2 << std::endl;
+}
+
+void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string refSketchOut, vector<sketch_t> &query_sketches,
+                string outputFile, int kmer_size, double maxDist, uint64_t maxNeighbor, bool isNeighbor, int isContainment, int numThreads) {
+    const double t0 = get_sec();
+    refuse64(ref_info, "index_dist()");
+    std::cerr << "-----not use hash64 in index_dist() " << std::endl;
+    IndexFiles ix;
+    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_dist()", ix);
+    std::vector<uint32_t> rflat, rsizes, qflat, qsizes;
+    std::vector<uint64_t> roff, qoff;
+    flatten(ref_sketches, rflat, roff, rsizes);
+    flatten(query_sketches, qflat, qoff, qsizes);
+    kssd_ctx *ctx = kssd_host::context();
+    check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, rsizes.data(), (uint32_t)rsizes.size()),
+          "index_load");
+    const double t1 = get_sec();
+    std::cerr << "===================time of read the index and dict sketch file is: " << t1 - t0 << std::endl;
+
+    const size_t numQuery = query_sketches.size();
+    if (numThreads < 1) numThreads = 1;
+    SubFiles sub(outputFile, numThreads);
+    std::cerr << "=====total: " << numQuery << std::endl;
+
+    // query rows are processed in blocks so that the hit list stays bounded when every cell passes (-D 1.0)
+    const size_t numRef = ref_sketches.size();
+    const size_t block = std::max<size_t>(1, std::min<size_t>(numQuery ? numQuery : 1, (size_t)(64u << 20) / std::max<size_t>(numRef, 1)));
+    for (size_t q0 = 0; q0 < numQuery; q0 += block) {
+        const size_t q1 = std::min(numQuery, q0 + block);
+        std::vector<kssd_hit> hits;
+        check(kssd_b200_dist_rows(ctx, qflat.data(), qoff.data(), (uint32_t)numQuery, KSSD_PTR_HOST, (uint32_t)q0, (uint32_t)q1, 0, kmer_size,
+                                  maxDist, isContainment, collect_hits, &hits),
+              "dist_rows");
+        std::vector<size_t> row_begin;
+        group_by_row(hits, numQuery, row_begin);
+#pragma omp parallel for num_threads(numThreads) schedule(static, 1)
+        for (int t = 0; t < numThreads; t++) {
+            std::string strBuf;
+            for (size_t i = q0 + ((t + numThreads - (int)(q0 % numThreads)) % numThreads); i < q1; i += numThreads) {  // rows with i % numThreads == t
+                fprintf(sub.fpIndexArr[t], "%s\t%s\n", query_sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
+                const int size1 = (int)qsizes[i];
+                priority_queue<DistInfo, vector<DistInfo>, cmpDistInfo> curQueue;  // dist.cpp:599
+                for (size_t k = row_begin[i]; k < row_begin[i + 1]; k++) {  // ascending ref index, as the reference's j loop
+                    const size_t j = hits[k].col;
+                    const int common = (int)hits[k].common, size0 = (int)rsizes[j];
+                    double jorc, d;
+                    exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
+                    if (!(d <= maxDist)) continue;  // inclusive, dist.cpp:624 / :661
+                    if (isNeighbor) {               // bounded max-heap, dist.cpp:625-640
+                        DistInfo di;
+                        di.refName = ref_sketches[j].fileName;
+                        di.common = common;
+                        di.refSize = size0;
+                        di.jorc = jorc;
+                        di.dist = d;
+                        if (curQueue.size() < maxNeighbor) curQueue.push(di);
+                        else if (d < curQueue.top().dist) {
+                            curQueue.push(di);
+                            curQueue.pop();
+                        }
+                    } else {
+                        strBuf += query_sketches[i].fileName + '\t' + ref_sketches[j].fileName + '\t' + to_string(common) + '|' + to_string(size0) +
+                                  '|' + to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
+                    }
+                }
+                while (!curQueue.empty()) {  // drained largest first, dist.cpp:683-689
+                    const DistInfo di = curQueue.top();
+                    strBuf += query_sketches[i].fileName + '\t' + di.refName + '\t' + to_string(di.common) + '|' + to_string(di.refSize) + '|' +
+                              to_string(size1) + '\t' + to_string(di.jorc) + '\t' + to_string(di.dist) + '\n';
+                    curQueue.pop();
+                }
+                if (strBuf.size() > (1u << 22)) {
+                    fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+                    strBuf.clear();
+                }
+            }
+            fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+        }
+    }
+    const double t2 = get_sec();
+    std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
+    sub.finish();
+    std::cerr << "===================time of merge the subFiles into final files is: " << get_sec() - t2 << std::endl;
+}

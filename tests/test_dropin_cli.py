@@ -1,0 +1,174 @@
+"""GPU: the drop-in CLI (reference main/subCommand/parsers/file I/O + the B200 shims behind the five hot functions)
+against the UNMODIFIED reference binary on identical inputs: .sketch hash sets, .dict/.index bytes, .alldist/.dist
+line sets (incl. -M 1, -N, FASTQ -Q/-n).  Both binaries are built by __graft_entry__.build() where the reference
+tree exists and travel to the GPU box; nothing here reads /root/reference."""
+import os
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+from rabbitkssd_b200 import formats, synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref", "rabbit_kssd")
+NEW = os.path.join(ROOT, "rabbitkssd_b200", "_dropin", "rabbit_kssd_b200")
+
+
+def _run(binary, args, cwd):
+    p = subprocess.run([binary] + args, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
+    assert p.returncode == 0, f"{os.path.basename(binary)} {' '.join(args)} failed:\n{p.stdout.decode()[-3000:]}"
+    return p.stdout.decode()
+
+
+def _sketch_sets(path):
+    _, names, sets = formats.read_sketch(path)
+    return {n: np.sort(s) for n, s in zip(names, sets)}
+
+
+@pytest.fixture(scope="module")
+def work(tmp_path_factory):
+    if not (os.access(REF, os.X_OK) and os.access(NEW, os.X_OK)):
+        pytest.skip("reference / drop-in binaries not built (run __graft_entry__.build() where the reference tree exists)")
+    d = str(tmp_path_factory.mktemp("dropin"))
+    data = os.path.join(d, "data")
+    os.makedirs(data)
+    # two families of related genomes + N runs / lowercase, 2-3 contigs each
+    refs, queries = [], []
+    for f in range(2):
+        fam = synth.family(4100 + f, 5, 400000, 0.05, n_contigs=2 + f)
+        for m, g in enumerate(fam):
+            g = [synth.sprinkle(c, 17 * f + m + ci, n_runs=4, run_len=9, lowercase_frac=0.02) for ci, c in enumerate(g)]
+            p = os.path.join(data, f"f{f}m{m}.fna")
+            synth.write_fasta(p, g, name=f"f{f}m{m}")
+            (refs if m < 4 else queries).append(p)
+    for i, p in enumerate(refs[:2]):  # queries that equal a reference and a fresh unrelated genome
+        queries.append(p)
+    extra = os.path.join(data, "lonely.fna")
+    synth.write_fasta(extra, [synth.random_bases(999, 250000)], name="lonely")
+    queries.append(extra)
+    # FASTQ reads of one genome
+    base = synth.random_bases(4242, 200000)
+    fq = []
+    for i in range(2):
+        n_reads, rl = 6000, 150
+        starts = (synth.splitmix64(77 + i, n_reads) % np.uint64(len(base) - rl)).astype(np.int64)
+        reads = [base[a:a + rl] for a in starts]
+        quals = [((synth.splitmix64(900 + 13 * i + r, rl) % np.uint64(41)) + 33).astype(np.uint8) for r in range(n_reads)]
+        p = os.path.join(data, f"reads{i}.fq")
+        synth.write_fastq(p, reads, quals, name=f"r{i}")
+        fq.append(p)
+    for name, lst in (("refs.list", refs), ("queries.list", queries), ("fq.list", fq)):
+        with open(os.path.join(d, name), "w") as f:
+            f.write("\n".join(lst) + "\n")
+    _run(REF, ["shuffle", "-k", "10", "-s", "6", "-l", "3", "-o", "L3K10.shuf"], d)
+    dirs = {}
+    for tag in ("ref", "new"):
+        dirs[tag] = os.path.join(d, tag)
+        os.makedirs(dirs[tag])
+    return {"d": d, "dirs": dirs, "bins": {"ref": REF, "new": NEW}}
+
+
+def _both(work, args):
+    for tag in ("ref", "new"):
+        _run(work["bins"][tag], args, work["dirs"][tag])
+
+
+def test_sketch_fasta_and_index_files(work):
+    d = work["d"]
+    _both(work, ["sketch", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"])
+    a = _sketch_sets(os.path.join(work["dirs"]["ref"], "refs.sketch"))
+    b = _sketch_sets(os.path.join(work["dirs"]["new"], "refs.sketch"))
+    assert sorted(a) == sorted(b)
+    for n in a:
+        assert len(a[n]) > 50 and np.array_equal(a[n], b[n]), n
+    # genome order inside the files may differ (the reference appends in thread-completion order): compare the
+    # inverted index as hash -> set of genome names
+    def inverted(tag):
+        _, names, _ = formats.read_sketch(os.path.join(work["dirs"][tag], "refs.sketch"))
+        counts, postings = formats.read_index_dict(os.path.join(work["dirs"][tag], "refs.sketch.index"),
+                                                   os.path.join(work["dirs"][tag], "refs.sketch.dict"))
+        nz = np.nonzero(counts)[0]
+        off = np.concatenate([[0], np.cumsum(counts[nz].astype(np.int64))]).astype(np.int64)
+        return {int(h): frozenset(names[g] for g in postings[off[i]:off[i + 1]]) for i, h in enumerate(nz)}, len(counts)
+    ia, na = inverted("ref")
+    ib, nb = inverted("new")
+    assert na == nb == 1 << 28
+    assert ia == ib
+
+
+def test_sketch_fastq_quality_and_count(work):
+    d = work["d"]
+    _both(work, ["sketch", "-q", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "fq.list"), "-o", "fq", "-Q", "35", "-n", "2",
+                 "-t", "2"])
+    a = _sketch_sets(os.path.join(work["dirs"]["ref"], "fq.sketch"))
+    b = _sketch_sets(os.path.join(work["dirs"]["new"], "fq.sketch"))
+    assert sorted(a) == sorted(b)
+    for n in a:
+        assert len(a[n]) > 5 and np.array_equal(a[n], b[n]), n
+
+
+@pytest.mark.parametrize("extra", [[], ["-M", "1"]])
+def test_alldist_from_same_sketch(work, extra):
+    """Same .sketch file in both directories: .dict/.index must be byte-identical, .alldist line sets equal."""
+    d = work["d"]
+    src = os.path.join(work["dirs"]["ref"], "refs.sketch")
+    if not os.path.exists(src):
+        _run(REF, ["sketch", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"], work["dirs"]["ref"])
+    for tag in ("ref", "new"):
+        for f in ("x.sketch", "x.sketch.index", "x.sketch.dict", "x.alldist"):
+            p = os.path.join(work["dirs"][tag], f)
+            if os.path.exists(p):
+                os.remove(p)
+        shutil.copy(src, os.path.join(work["dirs"][tag], "x.sketch"))
+    _both(work, ["alldist", "-i", "x.sketch", "-D", "0.08", "-o", "x.alldist", "-t", "3"] + extra)
+    for f in ("x.sketch.dict", "x.sketch.index"):
+        with open(os.path.join(work["dirs"]["ref"], f), "rb") as fa, open(os.path.join(work["dirs"]["new"], f), "rb") as fb:
+            assert fa.read() == fb.read(), f
+    la = sorted(formats.parse_dist_text(os.path.join(work["dirs"]["ref"], "x.alldist")))
+    lb = sorted(formats.parse_dist_text(os.path.join(work["dirs"]["new"], "x.alldist")))
+    assert len(la) >= 8
+    assert la == lb
+    with open(os.path.join(work["dirs"]["new"], "x.alldist")) as f:
+        assert f.readline() == " genome0\tgenome1\tcommon|size0|size1\tjaccard\tmashD\n"
+    assert not os.path.exists(os.path.join(work["dirs"]["new"], "x.alldist.dir"))
+
+
+@pytest.mark.parametrize("extra", [["-D", "0.1"], ["-N", "3"], ["-D", "0.3", "-N", "2", "-M", "1"], []])
+def test_dist_from_same_sketches(work, extra):
+    d = work["d"]
+    rdir = work["dirs"]["ref"]
+    if not os.path.exists(os.path.join(rdir, "refs.sketch")):
+        _run(REF, ["sketch", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"], rdir)
+    if not os.path.exists(os.path.join(rdir, "queries.sketch")):
+        _run(REF, ["sketch", "-q", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "queries.list"), "-o", "queries", "-t", "4"], rdir)
+    for tag in ("ref", "new"):
+        for f in ("r.sketch", "r.sketch.index", "r.sketch.dict", "q.sketch", "r.dist"):
+            p = os.path.join(work["dirs"][tag], f)
+            if os.path.exists(p):
+                os.remove(p)
+        shutil.copy(os.path.join(rdir, "refs.sketch"), os.path.join(work["dirs"][tag], "r.sketch"))
+        shutil.copy(os.path.join(rdir, "queries.sketch"), os.path.join(work["dirs"][tag], "q.sketch"))
+    _both(work, ["dist", "-r", "r.sketch", "-q", "q.sketch", "-o", "r.dist", "-t", "3"] + extra)
+    la = sorted(formats.parse_dist_text(os.path.join(work["dirs"]["ref"], "r.dist")))
+    lb = sorted(formats.parse_dist_text(os.path.join(work["dirs"]["new"], "r.dist")))
+    assert len(la) >= 4
+    assert la == lb
+
+
+def test_alldist_straight_from_genome_list(work):
+    """alldist -i <genome list>: sketch + index + distances in one command, each binary on its own sketches.
+    Line orientation (which genome is printed first) depends on the genome order inside the .sketch, which the
+    reference leaves to thread timing: compare unordered name pairs."""
+    d = work["d"]
+    _both(work, ["alldist", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "refs.list"), "-D", "0.08", "-o", "g.alldist", "-t", "4"])
+    def canon(tag):
+        out = []
+        for a, b, c, s0, s1, j, dd in formats.parse_dist_text(os.path.join(work["dirs"][tag], "g.alldist")):
+            out.append((frozenset([(a, s1), (b, s0)]), c, j, dd))
+        return sorted(out, key=lambda x: (sorted(x[0]), x[1]))
+    la, lb = canon("ref"), canon("new")
+    assert len(la) >= 8
+    assert la == lb
