@@ -339,12 +339,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     load_tile(tile, cur0, cur1);
 
     while (true) {
-        const uint32_t next_tile = tile + tile_stride;
-        uint4 nxt0 = make_uint4(0, 0, 0, 0), nxt1 = nxt0;
-        if (next_tile < a.n_tiles) load_tile(next_tile, nxt0, nxt1);
-
-        // ---- 32 bases -> 2 x 32 bits, previous lane's words as context ----
+        // ---- 32 bases -> 2 x 32 bits; the raw bytes are dead after this, so the SAME registers receive the next
+        //      tile right away (software pipelining without a second register set or copies) ----
         const uint32_t A0 = pack16_filter(cur0), A1 = pack16_filter(cur1);
+        const uint32_t this_tile = tile;
+        tile += tile_stride;
+        const bool more = tile < a.n_tiles;
+        if (more) load_tile(tile, cur0, cur1);
+        {   // pull the tile after that into L2 (one bulk prefetch per warp): the register prefetch above then pays
+            // L2 latency instead of HBM latency
+            const uint32_t far_tile = tile + tile_stride;
+            if (lane == 0 && far_tile < a.n_interior)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.seq + (size_t)far_tile * kTileBytes), "r"(1024) : "memory");
+        }
         const uint32_t P0 = __shfl_up_sync(FULL, A0, 1), P1 = __shfl_up_sync(FULL, A1, 1);
         // S = [P0, P1, A0, A1, 0] shifted so that bit 0 is the first index base of test 0
         uint32_t S0, S1, S2;
@@ -375,7 +382,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         // ---- queue the groups that passed (ballot + popc, no atomics); screen 32 at a time ----
         uint32_t any = __ballot_sync(FULL, hit != 0);
         if (any) {
-            const uint32_t lane_pos = tile * kTileBytes + lane_off_u;
+            const uint32_t lane_pos = this_tile * kTileBytes + lane_off_u;
             const uint4 sw = make_uint4(P0, P1, A0, A1);
             do {
                 if (hit) {
@@ -396,10 +403,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             } while (any);
         }
 
-        if (next_tile >= a.n_tiles) break;
-        tile = next_tile;
-        cur0 = nxt0;
-        cur1 = nxt1;
+        if (!more) break;
     }
     if (n_cand) stage1(0, n_cand);
     __syncwarp();
