@@ -133,7 +133,7 @@ void kssd_b200_destroy(kssd_ctx *c) {
     DevBuf *dev[] = {&c->d_bitmap, &c->d_tab_keys, &c->d_emit, &c->d_cursor, &c->d_stage_seq[0], &c->d_stage_seq[1],
                      &c->d_stage_qual[0], &c->d_stage_qual[1], &c->d_stage_segoff[0], &c->d_stage_segoff[1], &c->d_stage_seggen[0],
                      &c->d_stage_seggen[1], &c->d_sort_tmp, &c->d_sort_counts, &c->d_keys_unique, &c->d_hashes, &c->d_genome_off,
-                     &c->d_uniq_hash, &c->d_uniq_off, &c->d_dict, &c->d_ref_sizes, &c->d_pairs, &c->d_pairs_tmp, &c->d_q_hashes,
+                     &c->d_uniq_hash, &c->d_uniq_off, &c->d_dict, &c->d_ref_sizes, &c->d_pairs, &c->d_pairs_tmp, &c->d_bucket, &c->d_q_hashes,
                      &c->d_q_off, &c->d_q_list_begin, &c->d_q_list_end, &c->d_hits, &c->d_hit_cursor, &c->d_rowwork};
     for (DevBuf *b : dev) b->release();
     HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits};

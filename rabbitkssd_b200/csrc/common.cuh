@@ -115,6 +115,8 @@ struct kssd_ctx {
     uint32_t n_ref = 0;
     uint32_t max_ref_size = 0;
     kssd::DevBuf d_uniq_hash, d_uniq_off, d_dict, d_ref_sizes, d_pairs, d_pairs_tmp;
+    kssd::DevBuf d_bucket;    // bucket_start[b] = first distinct hash with (hash >> bucket_shift) >= b; 2^16 + 1 entries
+    int bucket_shift = 0;
     kssd::HostBuf h_uniq_hash, h_uniq_count, h_dict;
 
     // distances
@@ -140,6 +142,7 @@ int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_ge
 // index.cu
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
                        uint64_t total);
+int index_build_buckets(kssd_ctx *c);  // after d_uniq_hash / n_uniq are in place
 // dist.cu
 int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
                      uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,

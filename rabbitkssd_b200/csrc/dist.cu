@@ -20,6 +20,7 @@ namespace kssd {
 __global__ void __launch_bounds__(256) list_lookup_kernel(const uint32_t *__restrict__ q_hashes, const uint64_t *__restrict__ q_off,
                                                           uint32_t row_begin, uint32_t row_end, const uint32_t *__restrict__ uniq_hash,
                                                           const uint64_t *__restrict__ uniq_off, uint64_t n_uniq,
+                                                          const uint32_t *__restrict__ bucket, int bucket_shift,
                                                           const uint32_t *__restrict__ dict, int triangle,
                                                           uint32_t *__restrict__ lb, uint32_t *__restrict__ le,
                                                           unsigned long long *__restrict__ posting_total) {
@@ -28,7 +29,8 @@ __global__ void __launch_bounds__(256) list_lookup_kernel(const uint32_t *__rest
     uint32_t len = 0;
     if (e < e1) {
         uint32_t h = q_hashes[e];
-        uint64_t lo = 0, hi = n_uniq;
+        const uint32_t bk = min(h >> bucket_shift, 65535u);  // hashes above the largest indexed one fall into the last bucket
+        uint64_t lo = bucket[bk], hi = (h >> bucket_shift) > 65535u ? n_uniq : bucket[bk + 1];
         while (lo < hi) {
             uint64_t mid = (lo + hi) >> 1;
             if (uniq_hash[mid] < h) lo = mid + 1; else hi = mid;
@@ -214,7 +216,7 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     if (n_el) {
         list_lookup_kernel<<<(unsigned)((n_el + 255) / 256), 256, 0, st>>>(
             d_q_hashes, d_q_off, row_begin, row_end, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(), c->n_uniq,
-            c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
+            c->d_bucket.as<uint32_t>(), c->bucket_shift, c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
         KSSD_CUDA(cudaGetLastError());
         c->launches++;
     }

@@ -85,6 +85,41 @@ __global__ void __launch_bounds__(256) head_write_kernel(const uint64_t *__restr
 
 __global__ void set_u64_kernel(uint64_t *p, const uint64_t *idx, uint64_t v) { p[*idx] = v; }
 
+// Coarse directory over the sorted distinct hashes: a query hash is then found with ~5 binary-search steps inside
+// its bucket instead of ~21 over the whole array (list_lookup_kernel).
+static constexpr int kBucketBits = 16;
+__global__ void __launch_bounds__(256) bucket_start_kernel(const uint32_t *__restrict__ uniq_hash, uint64_t n_uniq, int shift,
+                                                           uint32_t *__restrict__ bucket) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > (1u << kBucketBits)) return;
+    uint64_t lo = 0, hi = n_uniq;  // first u with (uniq_hash[u] >> shift) >= b
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if ((uniq_hash[mid] >> shift) < b) lo = mid + 1; else hi = mid;
+    }
+    bucket[b] = (uint32_t)lo;
+}
+
+int index_build_buckets(kssd_ctx *c) {
+    cudaStream_t st = c->stream;
+    KSSD_TRY(c->d_bucket.reserve(((1u << kBucketBits) + 1) * 4, st));
+    uint32_t mx = 0;
+    if (c->n_uniq) {
+        KSSD_TRY(c->h_scalar.reserve(64));
+        KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, c->d_uniq_hash.as<uint32_t>() + (c->n_uniq - 1), 4, cudaMemcpyDeviceToHost, st));
+        KSSD_CUDA(cudaStreamSynchronize(st));
+        mx = *c->h_scalar.as<uint32_t>();
+    }
+    int bits = 0;
+    while (bits < 32 && (mx >> bits)) bits++;
+    c->bucket_shift = bits > kBucketBits ? bits - kBucketBits : 0;
+    bucket_start_kernel<<<((1u << kBucketBits) + 1 + 255) / 256, 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), c->n_uniq, c->bucket_shift,
+                                                                              c->d_bucket.as<uint32_t>());
+    KSSD_CUDA(cudaGetLastError());
+    c->launches++;
+    return KSSD_OK;
+}
+
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total) {
     cudaStream_t st = c->stream;
     c->have_index = false;
@@ -133,6 +168,7 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
         c->max_ref_size = 0;
     }
     c->n_uniq = n_uniq;
+    KSSD_TRY(index_build_buckets(c));
     c->have_index = true;
     return KSSD_OK;
 }

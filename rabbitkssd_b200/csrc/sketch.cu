@@ -34,7 +34,11 @@ struct ScanArgs {
     uint32_t first_emit;       // k-mers ending before this byte are context only
     const uint32_t *bitmap;    // membership bitmap followed by the second-level filter (copied to shared memory)
     const unsigned long long *table;  // exact retained-subset table: (dim_id << 32 | value), ~0 = empty
-    unsigned long long *emit;  // (position << 32 | hash); resolve_kernel turns positions into genome ids
+    unsigned long long *emit;  // (genome << 32 | hash)
+    const uint64_t *seg_off;   // segment table of the buffer (coordinates: byte 0 of this launch = pos_base)
+    const uint32_t *seg_genome;
+    uint32_t n_seg;
+    uint64_t pos_base;
     unsigned long long *cursor;
     uint64_t emit_cap;
     uint32_t n_tiles;
@@ -311,7 +315,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             unsigned long long at = 0;
             if (lane == 0) at = atomicAdd(a.cursor, (unsigned long long)__popc(m));
             at = __shfl_sync(FULL, at, 0) + __popc(m & lt);
-            if (ok && at < a.emit_cap) a.emit[at] = ((unsigned long long)p << 32) | hash;
+            if (ok && at < a.emit_cap) {
+                const uint64_t gpos = a.pos_base + p;
+                uint32_t lo = 0, hi = a.n_seg;  // owning segment: largest s with seg_off[s] <= pos
+                while (hi - lo > 1) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
+                }
+                a.emit[at] = ((unsigned long long)__ldg(a.seg_genome + lo) << 32) | hash;
+            }
         }
     };
     auto stage1 = [&](int base, int n) {  // screen queued groups [base, base+n), queue surviving positions for stage 2
@@ -408,36 +420,6 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     if (n_cand) stage1(0, n_cand);
     __syncwarp();
     if (n_ver) stage2(0, n_ver);
-}
-
-// (position << 32 | hash) -> (genome << 32 | hash) for the entries one scan launch appended: emit[*done .. *cursor)
-struct ResolveArgs {
-    unsigned long long *emit;
-    const unsigned long long *cursor;  // cursor[0] = appended so far, cursor[1] = resolved so far
-    uint64_t emit_cap;
-    const uint64_t *seg_off;
-    const uint32_t *seg_genome;
-    uint32_t n_seg;
-    uint64_t pos_base;  // position of the launch's byte 0 in the coordinates of seg_off
-};
-__global__ void __launch_bounds__(256) kssd_resolve_kernel(const ResolveArgs a) {
-    unsigned long long end = a.cursor[0];
-    if (end > a.emit_cap) end = a.emit_cap;
-    for (unsigned long long i = a.cursor[1] + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < end;
-         i += (unsigned long long)gridDim.x * blockDim.x) {
-        const unsigned long long e = a.emit[i];
-        const uint64_t gpos = (e >> 32) + a.pos_base;
-        uint32_t lo = 0, hi = a.n_seg;  // owning segment: largest s with seg_off[s] <= pos
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (a.seg_off[mid] <= gpos) lo = mid; else hi = mid;
-        }
-        a.emit[i] = ((unsigned long long)a.seg_genome[lo] << 32) | (e & 0xFFFFFFFFull);
-    }
-}
-__global__ void kssd_commit_kernel(unsigned long long *cursor, uint64_t emit_cap) {
-    unsigned long long c = cursor[0];
-    cursor[1] = c < emit_cap ? c : emit_cap;
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------
@@ -567,6 +549,9 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.bitmap = c->d_bitmap.as<uint32_t>();
     a.table = c->d_tab_keys.as<unsigned long long>();
     a.emit = c->d_emit.as<unsigned long long>();
+    a.seg_off = d_seg_off;
+    a.seg_genome = d_seg_genome;
+    a.n_seg = n_seg;
     a.cursor = c->d_cursor.as<unsigned long long>();
     a.emit_cap = c->emit_cap;
     a.sp = sp;
@@ -583,6 +568,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         const uint64_t b1 = std::min<uint64_t>(n_bytes, b0 + kMaxPiece);
         const uint64_t from = b0 ? b0 - halo : 0;
         a.seq = d_seq + from;
+        a.pos_base = pos_base + from;
         a.aligned32 = (reinterpret_cast<uintptr_t>(a.seq) & 31) == 0;
         a.qual = use_qual ? d_qual + from : nullptr;
         a.n_bytes = (uint32_t)(b1 - from);
@@ -600,18 +586,6 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         default: set_error("bad filter group %d", sp.group); return KSSD_E_ARG;
         }
         KSSD_TRY(rc);
-        ResolveArgs ra;
-        ra.emit = a.emit;
-        ra.cursor = a.cursor;
-        ra.emit_cap = a.emit_cap;
-        ra.seg_off = d_seg_off;
-        ra.seg_genome = d_seg_genome;
-        ra.n_seg = n_seg;
-        ra.pos_base = pos_base + from;
-        kssd_resolve_kernel<<<c->sm_count * 2, 256, 0, c->stream>>>(ra);
-        kssd_commit_kernel<<<1, 1, 0, c->stream>>>(a.cursor, a.emit_cap);
-        KSSD_CUDA(cudaGetLastError());
-        c->launches += 2;
     }
     return KSSD_OK;
 }
