@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--family", type=int, default=10)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--phases", action="store_true", help="diagnostic: per-phase wall times (synchronised) on stderr after the timed runs")
     ap.add_argument("--cpu-sample-genomes", type=int, default=256)
     return ap.parse_args()
 
@@ -255,7 +256,11 @@ def run_b200(args):
     stride = (length + 2 + 15) // 16 * 16
 
     ctx = api.Context(local_rank)
-    stream = torch.cuda.current_stream()
+    # ONE explicit (non-default) stream for torch, NCCL and the library: handle 0 (the legacy default stream) means
+    # "library-owned stream" to kssd_b200_set_stream, and torch ops on stream 0 would then race with the kernels
+    stream = torch.cuda.Stream(device=local_rank)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ctx.set_stream(stream.cuda_stream)
     dim = oracle.shuffle_dim(K, S, L_)  # the .shuf table is an INPUT of the path (glibc-rand permutation)
     ctx.set_params(K, S, L_, dim)
@@ -271,8 +276,22 @@ def run_b200(args):
     r0, r1 = bounds[rank], bounds[rank + 1]
     state = {}
 
+    phase_t = {}
+
+    def mark(name, t0):
+        if args.phases and state.get("diag"):
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            phase_t[name] = phase_t.get(name, 0.0) + (t1 - t0) * 1e3
+            return t1
+        return t0
+
     def finish_and_dist(keep=False):
+        t0 = mark("scan", state.get("t_step0", 0.0))
         d_h, d_o, tot = ctx.sketch_finish_device()
+        if state.setdefault("tot0", tot) != tot:  # the sketch of a fixed input must not change between steps
+            raise RuntimeError(f"rank {rank}: sketch size changed between steps: {state['tot0']} -> {tot}")
+        t0 = mark("sort_unique", t0)
         if world > 1:
             h_loc = dev_tensor(torch, d_h, tot, torch.int32)
             o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
@@ -293,12 +312,18 @@ def run_b200(args):
             state["keep"] = (hashes, off)
         else:
             ph, po = d_h, d_o
+        t0 = mark("gather", t0)
         ctx.index_build_device(ph, po, n_total)
+        t0 = mark("index", t0)
         d_hits, n_hits = ctx.dist_rows_device(ph, po, n_total, True, 2 * K, MAX_DIST, 0, rows=(r0, r1))
+        t0 = mark("dist", t0)
         state.update(d_hits=d_hits, n_hits=n_hits, ph=ph, po=po)
         return n_hits
 
     def step_device():
+        if args.phases and state.get("diag"):
+            torch.cuda.synchronize()
+            state["t_step0"] = time.perf_counter()
         ctx.sketch_begin(n_local)
         ctx.scan_device(buf.data_ptr(), n_bytes, d_seg_off.data_ptr(), d_seg_gen.data_ptr(), n_local)
         return finish_and_dist()
@@ -334,6 +359,13 @@ def run_b200(args):
     ms_per_step = ms / args.steps
     pairs = n_total * (n_total - 1) / 2.0
     value = pairs / (ms_per_step / 1e3)
+
+    if args.phases:
+        state["diag"] = True
+        for _ in range(3):
+            step_device()
+        state["diag"] = False
+        sys.stderr.write("phases rank %d (ms/step, synchronised): %s\n" % (rank, json.dumps({k: round(v / 3, 3) for k, v in phase_t.items()})))
 
     # ---- end to end: pinned host buffers -> C-ABI (H2D inside the timed region) -> hits read back ----
     host = torch.empty(n_bytes, dtype=torch.uint8, pin_memory=True)

@@ -38,7 +38,9 @@ int kssd_b200_version(void);
 /* Create a context on CUDA device `device`.  Fails (KSSD_E_CUDA) when no device is usable. */
 int kssd_b200_init(kssd_ctx **ctx, int device);
 void kssd_b200_destroy(kssd_ctx *ctx);
-/* Run all work of this ctx on the caller's cudaStream_t (e.g. torch's current stream); NULL = own stream. */
+/* Run all work of this ctx on the caller's cudaStream_t (e.g. a torch.cuda.Stream); NULL = library-owned
+ * non-blocking stream.  The legacy default stream has handle 0 and therefore cannot be passed: callers that mix
+ * their own kernels with the library's must create an explicit stream. */
 int kssd_b200_set_stream(kssd_ctx *ctx, void *cuda_stream);
 int kssd_b200_sync(kssd_ctx *ctx);
 
