@@ -88,6 +88,16 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+def measured_traffic_ratio():
+    """DRAM bytes per input byte of the scan kernel from the committed `ncu --set full` capture (profiles/)."""
+    p = os.path.join(ROOT, "profiles", "scan_traffic.json")
+    try:
+        d = json.load(open(p))
+        return float(d["dram_bytes_per_input_byte"]), d["capture"]
+    except Exception:
+        return None, None
+
+
 def measured_hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -224,23 +234,11 @@ def gen_genomes_device(torch, n_local, first_genome, length, family, stride):
     return buf
 
 
-def triangle_bounds(n, parts):
-    """Row boundaries that give every part the same number of (row, col>row) cells."""
-    total = n * (n - 1) / 2.0
-    b = [0]
-    for p in range(1, parts):
-        target = total * p / parts
-        # cells in rows [0, r) = r*n - r(r+1)/2  -> solve for r
-        r = int(round(((2 * n - 1) - ((2 * n - 1) ** 2 - 8 * target) ** 0.5) / 2))
-        b.append(min(max(r, b[-1]), n))
-    b.append(n)
-    return b
-
-
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from rabbitkssd_b200 import api
+    from rabbitkssd_b200.multigpu import gather_sketches, triangle_bounds
     import oracle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -295,19 +293,7 @@ def run_b200(args):
         if world > 1:
             h_loc = dev_tensor(torch, d_h, tot, torch.int32)
             o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
-            sizes_loc = (o_loc[1:] - o_loc[:-1]).contiguous()
-            sizes_all = torch.empty(n_total, dtype=torch.int64, device="cuda")
-            dist.all_gather_into_tensor(sizes_all, sizes_loc)
-            tots = sizes_all.view(world, n_local).sum(1)
-            tots_h = tots.cpu()
-            mx = int(tots_h.max())
-            pad = torch.zeros(mx, dtype=torch.int32, device="cuda")
-            pad[:tot] = h_loc
-            allh = torch.empty(world * mx, dtype=torch.int32, device="cuda")
-            dist.all_gather_into_tensor(allh, pad)
-            hashes = torch.cat([allh[i * mx:i * mx + int(tots_h[i])] for i in range(world)])
-            off = torch.zeros(n_total + 1, dtype=torch.int64, device="cuda")
-            off[1:] = torch.cumsum(sizes_all, 0)
+            hashes, off = gather_sketches(dist, h_loc, o_loc[1:] - o_loc[:-1], world)
             ph, po = hashes.data_ptr(), off.data_ptr()
             state["keep"] = (hashes, off)
         else:
@@ -410,6 +396,7 @@ def run_b200(args):
     # emitted keys ~ unique hashes (duplicates inside a 5 Mbp genome are negligible)
     alg_bytes = scan_bytes / max(scan_n, 1) + 8.0 * (hashes_total / world) / max(scan_n / max(args.steps, 1), 1)
     scan_ms_per = scan_ms / max(scan_n, 1)
+    t_ratio, t_src = measured_traffic_ratio()
     achieved = alg_bytes / (scan_ms_per / 1e3) / 1e9 if scan_ms_per > 0 else 0.0
     out = {
         "metric": "alldist genome-pairs/s (sketch + index + alldist of the whole genome set)", "value": value,
@@ -428,7 +415,8 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "roofline": {"bound": "hbm", "kernel": "kssd_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak,
+                     "traffic": (t_ratio * scan_bytes / max(scan_n, 1)) if t_ratio else None, "traffic_source": t_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": scan_ms_per,
                      "share_of_step": scan_ms / ms if ms else None},
         "alldist_kernel": {"ms_per_launch": cnt_ms / max(cnt_n, 1), "postings_per_s": cnt_post / (cnt_ms / 1e3) if cnt_ms else None,

@@ -6,20 +6,27 @@
 // integer instructions and an exact path that only sees the <1% of positions the filter lets through:
 //
 //   filter (every base)
-//   * a lane owns 32 bases: two 128-bit coalesced loads; lane 0 of the warp re-reads the 32 bases before the
-//     tile as halo, so no state is carried between tiles (tile = 31 x 32 = 992 new bytes per warp);
+//   * a lane owns 32 bases: one 256-bit load (LDG.E.256), the next tile is loaded into the same registers as soon
+//     as the bytes are packed and the tile after that is pulled into L2 with one bulk prefetch per warp; lane 0
+//     of the warp re-reads the 32 bases before the tile as halo, so no state is carried between tiles
+//     (tile = 31 x 32 = 992 new bytes per warp);
 //   * 4 ASCII bytes -> 8 bits with one AND and one IMAD ((x & 0x06060606) * M gathers bits 1-2 of each byte:
 //     A/a 0, C/c 1, T/t 2, G/g 3).  Validity (N, separators, quality) is NOT decided here;
 //   * membership of the 2s-mer is tested WITHOUT deciding the canonical strand and for G consecutive k-mer end
 //     positions at once: the shared-memory bitmap holds, for every retained 2s-mer and its reverse complement,
 //     one bit per alignment g < G of the 2s-mer against the bases that all G windows have in common (up to 10
 //     bases = 20 index bits).  One funnel shift, one shift+mask, one LDS, two shifts decide G positions;
-//   * groups that pass are appended to a per-warp shared-memory queue (ballot + popc, no atomics).
-//   exact path (queued groups, 32 at a time, one per lane)
-//   * re-reads the 2k+G-1 raw bytes of the group (three 128-bit loads), decodes them with the reference's
-//     BaseMap semantics (common.h:27-37), checks validity of each window, then runs the reference's 64-bit
-//     arithmetic: canonical min of tuple / reverse complement, dim_id, exact retained-subset lookup, hash
-//     composition (sketch.cpp:508-524), quality check (sketch.cpp:280) only for survivors, append to the emit buffer.
+//   * groups that pass are appended to a per-warp shared-memory queue (ballot + popc, no atomics) together with
+//     the lane's packed words [P0,P1,A0,A1].
+//   stage 1 (queued groups, 32 at a time, one per lane; no memory traffic)
+//   * canonical dim_id of each of the group's G positions from the packed words, looked up in a second-level
+//     shared-memory filter (2^18 bits indexed by a hash of the full dim_id); survivors go to a second queue.
+//   stage 2 (queued positions, 32 at a time, one per lane; the exact path)
+//   * re-reads the 2k raw bytes of the k-mer (three 128-bit loads + a select network), decodes them with the
+//     reference's BaseMap semantics (common.h:27-37), checks validity of the whole window, then runs the
+//     reference's 64-bit arithmetic: canonical min of tuple / reverse complement, dim_id, exact retained-subset
+//     lookup, hash composition (sketch.cpp:508-524), quality check (sketch.cpp:280) for survivors only, owning
+//     genome by binary search in the segment table, one warp-aggregated atomic append to the emit buffer.
 #include <algorithm>
 #include <cstring>
 

@@ -1,0 +1,54 @@
+"""Host-side logic of the multi-GPU path: one process per GPU, torch.distributed for plumbing only.
+
+The distance path shards by query rows with a replicated index (src/dist.cpp:174-258 / :560-692 have no cross-row
+state), so the only exchange is the all-gather of the per-rank sketch shards before the index is built.  Everything
+here is plain torch on whatever device the tensors live on, so the same code runs under NCCL on B200s and under
+gloo on CPUs (tests/test_multirank_gloo.py)."""
+import torch
+
+
+def triangle_bounds(n, parts):
+    """Row boundaries b[0..parts] that give every part (nearly) the same number of (row, col > row) cells of the
+    n x n triangle: row i costs n-1-i cells (src/dist.cpp:207 scans j in (i, n))."""
+    total = n * (n - 1) / 2.0
+    b = [0]
+    for p in range(1, parts):
+        target = total * p / parts
+        # cells in rows [0, r) = r*n - r(r+1)/2  -> solve for r
+        r = int(round(((2 * n - 1) - ((2 * n - 1) ** 2 - 8 * target) ** 0.5) / 2))
+        b.append(min(max(r, b[-1]), n))
+    b.append(n)
+    return b
+
+
+def rect_bounds(n_query, parts):
+    """dist (query x ref rectangle): contiguous blocks of query rows, sizes differing by at most one."""
+    base, extra = divmod(n_query, parts)
+    b = [0]
+    for p in range(parts):
+        b.append(b[-1] + base + (1 if p < extra else 0))
+    return b
+
+
+def gather_sketches(dist, hashes_local, sizes_local, world):
+    """All-gather of CSR sketch shards.  hashes_local: int32[total_local] (the u32 hashes, bit-cast), sizes_local:
+    int64[n_local] per-genome sketch sizes; every rank holds the same number of genomes.  Returns
+    (hashes int32[total], off int64[n_total+1]) in rank order, identical on every rank."""
+    n_local = sizes_local.numel()
+    dev = hashes_local.device
+    if world == 1:
+        off = torch.zeros(n_local + 1, dtype=torch.int64, device=dev)
+        off[1:] = torch.cumsum(sizes_local, 0)
+        return hashes_local, off
+    sizes_all = torch.empty(world * n_local, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(sizes_all, sizes_local.contiguous())
+    tots = sizes_all.view(world, n_local).sum(1).cpu()
+    mx = int(tots.max())
+    pad = torch.zeros(mx, dtype=torch.int32, device=dev)
+    pad[:hashes_local.numel()] = hashes_local
+    allh = torch.empty(world * mx, dtype=torch.int32, device=dev)
+    dist.all_gather_into_tensor(allh, pad)
+    hashes = torch.cat([allh[i * mx:i * mx + int(tots[i])] for i in range(world)])
+    off = torch.zeros(world * n_local + 1, dtype=torch.int64, device=dev)
+    off[1:] = torch.cumsum(sizes_all, 0)
+    return hashes, off
