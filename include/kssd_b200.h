@@ -133,6 +133,11 @@ int kssd_b200_index_adopt_device(kssd_ctx *ctx, uint64_t n_uniq, uint64_t total,
  *   triangle = 1: alldist, only cols > row (dist.cpp:207), strict  `<`  (dist.cpp:232);
  *   triangle = 0: dist, all cols, inclusive `<=` (dist.cpp:624). */
 typedef struct kssd_hit { uint32_t row, col, common; } kssd_hit;
+/* A cell with common == 0 has distance exactly 1.0 (dist.cpp:227-228), so with -D >= 1 (the CLI default) EVERY cell
+ * passes and the hit list is the dense rows x cols matrix.  on = 0 makes the device report only cells with
+ * common > 0; the caller then knows that every unreported cell has common == 0, Jaccard 0 and distance 1
+ * (dist_gpu.cpp fills them in, in reference order, where the threshold lets them pass).  Default: on = 1. */
+int kssd_b200_set_emit_zero_cells(kssd_ctx *ctx, int on);
 typedef int (*kssd_sink)(void *user, const kssd_hit *hits, size_t n);
 int kssd_b200_dist_rows(kssd_ctx *ctx, const uint32_t *q_hashes, const uint64_t *q_off, uint32_t n_query,
                         int ptr_kind, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size,

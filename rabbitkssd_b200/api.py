@@ -182,6 +182,9 @@ class Context:
                                                     C.c_void_p(d_uniq_off), C.c_void_p(d_dict), C.c_void_p(d_ref_sizes)))
 
     # ---- distances ----
+    def set_emit_zero_cells(self, on=True):
+        check(self.lib.kssd_b200_set_emit_zero_cells(self.h, int(on)))
+
     def dist_rows(self, q_hashes, q_off, triangle, kmer_size, max_dist, containment=0, rows=None):
         """-> structured hits (row, col, common) that pass the device's conservative test (host refines)."""
         q_hashes = np.ascontiguousarray(q_hashes, dtype=np.uint32)

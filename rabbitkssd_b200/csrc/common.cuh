@@ -120,6 +120,7 @@ struct kssd_ctx {
     kssd::HostBuf h_uniq_hash, h_uniq_count, h_dict;
 
     // distances
+    bool emit_zero_cells = true;  // report cells with common == 0 when they pass the threshold (kssd_b200_set_emit_zero_cells)
     kssd::DevBuf d_q_hashes, d_q_off, d_q_list_begin, d_q_list_end, d_hits, d_hit_cursor, d_rowwork;
     kssd::HostBuf h_hits;
 

@@ -256,7 +256,7 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     a.triangle = triangle;
     a.containment = containment;
     // distance of a zero cell is exactly 1.0 (dist.cpp:227-228): strict '<' for alldist, '<=' for dist
-    a.zero_pass = triangle ? (1.0 < max_dist) : (1.0 <= max_dist);
+    a.zero_pass = c->emit_zero_cells && (triangle ? (1.0 < max_dist) : (1.0 <= max_dist));
     a.neg_inv_k = -1.0 / kmer_size;
     a.dist_limit = max_dist + std::fabs(max_dist) * 1e-9 + 1e-12;
     a.hit_cursor = d_cursor;

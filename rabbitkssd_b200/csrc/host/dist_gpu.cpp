@@ -170,6 +170,23 @@ struct SubFiles {
     }
 };
 
+// Cells of one row in ascending column order, as the reference's j loop sees them.  The device reports only cells
+// with common > 0 (kssd_b200_set_emit_zero_cells(ctx, 0)); when `dense` is set (a zero cell, distance exactly 1.0,
+// passes the threshold) the unreported columns of [jbegin, jend) are visited too, with common = 0.
+template <typename F>
+inline void for_each_cell(const std::vector<kssd_hit> &hits, size_t kb, size_t ke, size_t jbegin, size_t jend, bool dense, F &&fn) {
+    if (!dense) {
+        for (size_t k = kb; k < ke; k++) fn((size_t)hits[k].col, (int)hits[k].common);
+        return;
+    }
+    size_t k = kb;
+    for (size_t j = jbegin; j < jend; j++) {
+        int common = 0;
+        if (k < ke && hits[k].col == j) common = (int)hits[k++].common;
+        fn(j, common);
+    }
+}
+
 void refuse64(const sketchInfo_t &info, const char *who) {
     if (info.half_k - info.drlevel > 8) {
         fprintf(stderr, "ERROR: %s: the 64-bit hash path is not implemented in the B200 build\n", who);
@@ -208,6 +225,8 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
     SubFiles sub(outputFile, numThreads);
     std::cerr << "=====total: " << numRef << std::endl;
     std::vector<kssd_hit> hits;
+    check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
+    const bool dense = 1.0 < maxDist;  // zero cells pass `mashD < maxDist` (dist.cpp:227-232)
     check(kssd_b200_dist_rows(ctx, flat.data(), off.data(), (uint32_t)numRef, KSSD_PTR_HOST, 0, (uint32_t)numRef, 1, kmer_size, maxDist,
                               isContainment, collect_hits, &hits),
           "dist_rows");
@@ -219,15 +238,18 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
         std::string strBuf;
         for (size_t i = t; i < numRef; i += numThreads) {
             fprintf(sub.fpIndexArr[t], "%s\t%s\n", sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
-            for (size_t k = row_begin[i]; k < row_begin[i + 1]; k++) {
-                const size_t j = hits[k].col;
-                const int common = (int)hits[k].common, size0 = (int)sizes[i], size1 = (int)sizes[j];
+            for_each_cell(hits, row_begin[i], row_begin[i + 1], i + 1, numRef, dense, [&](size_t j, int common) {
+                const int size0 = (int)sizes[i], size1 = (int)sizes[j];
                 double jorc, d;
                 exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
                 if (d < maxDist)  // strict, dist.cpp:232 / :251
                     strBuf += sketches[j].fileName + '\t' + sketches[i].fileName + '\t' + to_string(common) + '|' + to_string(size0) + '|' +
                               to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
-            }
+                if (strBuf.size() > (1u << 22)) {
+                    fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+                    strBuf.clear();
+                }
+            });
             if (strBuf.size() > (1u << 22)) {
                 fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
                 strBuf.clear();
@@ -265,6 +287,8 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
 
     // query rows are processed in blocks so that the hit list stays bounded when every cell passes (-D 1.0)
     const size_t numRef = ref_sketches.size();
+    check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
+    const bool dense = 1.0 <= maxDist;  // zero cells pass `mashD <= maxDist` (dist.cpp:621-624)
     const size_t block = std::max<size_t>(1, std::min<size_t>(numQuery ? numQuery : 1, (size_t)(64u << 20) / std::max<size_t>(numRef, 1)));
     for (size_t q0 = 0; q0 < numQuery; q0 += block) {
         const size_t q1 = std::min(numQuery, q0 + block);
@@ -281,12 +305,11 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
                 fprintf(sub.fpIndexArr[t], "%s\t%s\n", query_sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
                 const int size1 = (int)qsizes[i];
                 priority_queue<DistInfo, vector<DistInfo>, cmpDistInfo> curQueue;  // dist.cpp:599
-                for (size_t k = row_begin[i]; k < row_begin[i + 1]; k++) {  // ascending ref index, as the reference's j loop
-                    const size_t j = hits[k].col;
-                    const int common = (int)hits[k].common, size0 = (int)rsizes[j];
+                for_each_cell(hits, row_begin[i], row_begin[i + 1], 0, numRef, dense, [&](size_t j, int common) {  // ascending ref index
+                    const int size0 = (int)rsizes[j];
                     double jorc, d;
                     exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
-                    if (!(d <= maxDist)) continue;  // inclusive, dist.cpp:624 / :661
+                    if (!(d <= maxDist)) return;  // inclusive, dist.cpp:624 / :661
                     if (isNeighbor) {               // bounded max-heap, dist.cpp:625-640
                         DistInfo di;
                         di.refName = ref_sketches[j].fileName;
@@ -302,8 +325,12 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
                     } else {
                         strBuf += query_sketches[i].fileName + '\t' + ref_sketches[j].fileName + '\t' + to_string(common) + '|' + to_string(size0) +
                                   '|' + to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
+                        if (strBuf.size() > (1u << 22)) {
+                            fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
+                            strBuf.clear();
+                        }
                     }
-                }
+                });
                 while (!curQueue.empty()) {  // drained largest first, dist.cpp:683-689
                     const DistInfo di = curQueue.top();
                     strBuf += query_sketches[i].fileName + '\t' + di.refName + '\t' + to_string(di.common) + '|' + to_string(di.refSize) + '|' +

@@ -110,8 +110,8 @@ def test_sketch_fastq_quality_and_count(work):
         assert len(a[n]) > 5 and np.array_equal(a[n], b[n]), n
 
 
-@pytest.mark.parametrize("extra", [[], ["-M", "1"]])
-def test_alldist_from_same_sketch(work, extra):
+@pytest.mark.parametrize("D,extra", [("0.08", []), ("0.08", ["-M", "1"]), ("1.5", [])])
+def test_alldist_from_same_sketch(work, D, extra):
     """Same .sketch file in both directories: .dict/.index must be byte-identical, .alldist line sets equal."""
     d = work["d"]
     src = os.path.join(work["dirs"]["ref"], "refs.sketch")
@@ -123,7 +123,7 @@ def test_alldist_from_same_sketch(work, extra):
             if os.path.exists(p):
                 os.remove(p)
         shutil.copy(src, os.path.join(work["dirs"][tag], "x.sketch"))
-    _both(work, ["alldist", "-i", "x.sketch", "-D", "0.08", "-o", "x.alldist", "-t", "3"] + extra)
+    _both(work, ["alldist", "-i", "x.sketch", "-D", D, "-o", "x.alldist", "-t", "3"] + extra)  # -D 1.5: every pair, also common = 0
     for f in ("x.sketch.dict", "x.sketch.index"):
         with open(os.path.join(work["dirs"]["ref"], f), "rb") as fa, open(os.path.join(work["dirs"]["new"], f), "rb") as fb:
             assert fa.read() == fb.read(), f
