@@ -75,15 +75,22 @@ __global__ void radix_scan_digits_kernel(uint32_t *totals, uint64_t *digit_base)
 
 // Stable scatter.  Warp w owns keys [w*512, (w+1)*512) of the tile and walks them 32 at a time in order;
 // __match_any_sync groups equal digits inside a 32-key row, a per-warp shared counter carries the running count.
+// Keys are first placed at their tile-local sorted position in shared memory and then written out in that order, so
+// that consecutive threads write consecutive addresses of the same digit run (coalesced) instead of 8-byte
+// scattered stores.
 __global__ void __launch_bounds__(kRadixThreads) radix_scatter_kernel(const uint64_t *__restrict__ keys, uint64_t *__restrict__ out,
                                                                       uint64_t n, int shift, const uint32_t *__restrict__ counts,
                                                                       const uint64_t *__restrict__ digit_base, uint32_t n_tiles) {
+    __shared__ uint64_t skeys[kRadixTile];
     __shared__ uint32_t wcount[kWarps][256];
-    __shared__ uint64_t dbase[256];
+    __shared__ uint32_t tstart[256];   // tile-local start of each digit run
+    __shared__ uint64_t gbase[256];    // global position of the first key of this tile's digit run
+    __shared__ uint32_t wsum[kWarps];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < kWarps * 256; i += kRadixThreads) (&wcount[0][0])[i] = 0;
     __syncthreads();
-    uint64_t wbase = (uint64_t)blockIdx.x * kRadixTile + (uint64_t)w * (32 * kRadixItems);
+    const uint64_t tbase = (uint64_t)blockIdx.x * kRadixTile;
+    const uint64_t wbase = tbase + (uint64_t)w * (32 * kRadixItems);
     uint64_t key[kRadixItems];
     uint32_t rank[kRadixItems];
     const uint32_t lt = (1u << lane) - 1;
@@ -106,13 +113,24 @@ __global__ void __launch_bounds__(kRadixThreads) radix_scatter_kernel(const uint
         __syncwarp();
     }
     __syncthreads();
-    // exclusive prefix over warps per digit + global base of this tile's digit run
+    // per digit: exclusive prefix over warps, tile total; then exclusive scan of the totals over the 256 digits
     {
-        int d = threadIdx.x;
+        const int d = threadIdx.x;
         uint32_t acc = 0;
 #pragma unroll
         for (int k = 0; k < kWarps; k++) { uint32_t v = wcount[k][d]; wcount[k][d] = acc; acc += v; }
-        dbase[d] = digit_base[d] + counts[(uint64_t)d * n_tiles + blockIdx.x];
+        uint32_t x = acc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) wsum[w] = x;
+        __syncthreads();
+        uint32_t wp = 0;
+        for (int k = 0; k < w; k++) wp += wsum[k];
+        tstart[d] = wp + x - acc;
+        gbase[d] = digit_base[d] + counts[(uint64_t)d * n_tiles + blockIdx.x];
     }
     __syncthreads();
 #pragma unroll
@@ -120,8 +138,15 @@ __global__ void __launch_bounds__(kRadixThreads) radix_scatter_kernel(const uint
         uint64_t i = wbase + r * 32 + lane;
         if (i < n) {
             uint32_t d = (uint32_t)(key[r] >> shift) & 255;
-            out[dbase[d] + wcount[w][d] + rank[r]] = key[r];
+            skeys[tstart[d] + wcount[w][d] + rank[r]] = key[r];
         }
+    }
+    __syncthreads();
+    const uint32_t n_tile = (uint32_t)min((uint64_t)kRadixTile, n - tbase);
+    for (uint32_t i = threadIdx.x; i < n_tile; i += kRadixThreads) {
+        const uint64_t k = skeys[i];
+        const uint32_t d = (uint32_t)(k >> shift) & 255;
+        out[gbase[d] + (i - tstart[d])] = k;
     }
 }
 
