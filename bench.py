@@ -67,7 +67,7 @@ class ClockSampler:
                     self.samples.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self.stop.wait(0.15)
+            self.stop.wait(0.03)
 
     def __enter__(self):
         self.t.start()
@@ -319,14 +319,16 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    ctx.scan_kernel_time()
-    ctx.count_kernel_time()
-    launches0 = ctx.launch_count()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # clocks are sampled over warm-up + timed steps (the same load): the timed region alone can be shorter than one
+    # nvidia-smi poll
     with ClockSampler(local_rank) as clk:
+        for _ in range(max(args.warmup, 3)):
+            step_device()
+        ctx.scan_kernel_time()
+        ctx.count_kernel_time()
+        launches0 = ctx.launch_count()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(args.steps):
             n_hits = step_device()

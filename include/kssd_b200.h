@@ -151,6 +151,9 @@ int kssd_b200_dist_rows_device(kssd_ctx *ctx, const uint32_t *d_q_hashes, const 
 /* ---- introspection for bench.py / tests ---------------------------------------------------------------- */
 /* Bracket the scan / count kernels with CUDA events on the ctx stream (off by default). */
 int kssd_b200_set_profiling(kssd_ctx *ctx, int on);
+/* Tests: on = 1 takes the device-wide radix-sort paths even where the shared-memory segment sorts apply (per-genome
+ * sort + unique, index build), so that both implementations are checked against the oracle. */
+int kssd_b200_set_force_radix(kssd_ctx *ctx, int on);
 /* Number of kernels this ctx has launched since init (bench.py's gpu_launches). */
 uint64_t kssd_b200_launch_count(kssd_ctx *ctx);
 /* Time (ms, CUDA events on the ctx stream) and launch count of the scan kernel since the last call. */

@@ -34,6 +34,7 @@ SYMBOLS = {
     "kssd_b200_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "kssd_b200_sync": (C.c_int, [C.c_void_p]),
     "kssd_b200_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
+    "kssd_b200_set_force_radix": (C.c_int, [C.c_void_p, C.c_int]),
     "kssd_b200_set_params": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, i32p]),
     "kssd_b200_sketch_begin": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int]),
     "kssd_b200_batch_acquire": (C.c_int, [C.c_void_p, C.POINTER(C.POINTER(Batch)), C.c_uint64, C.c_uint32]),

@@ -45,6 +45,10 @@ class Context:
     def set_profiling(self, on=True):
         check(self.lib.kssd_b200_set_profiling(self.h, int(on)))
 
+    def set_force_radix(self, on=True):
+        """Tests: take the device-wide radix paths even where the shared-memory segment sorts apply."""
+        check(self.lib.kssd_b200_set_force_radix(self.h, int(on)))
+
     def launch_count(self):
         return int(self.lib.kssd_b200_launch_count(self.h))
 

@@ -179,6 +179,12 @@ int kssd_b200_set_profiling(kssd_ctx *c, int on) {
     return KSSD_OK;
 }
 
+int kssd_b200_set_force_radix(kssd_ctx *c, int on) {
+    KSSD_TRY(check_ctx(c));
+    c->force_radix = on != 0;
+    return KSSD_OK;
+}
+
 int kssd_b200_set_params(kssd_ctx *c, int half_k, int half_subk, int drlevel, const int32_t *shuffled_dim) {
     KSSD_TRY(check_ctx(c));
     if (!shuffled_dim) { set_error("set_params: null shuffle table"); return KSSD_E_ARG; }

@@ -83,6 +83,7 @@ struct kssd_ctx {
     cudaStream_t copy_stream = nullptr;
     uint64_t launches = 0;
     bool profiling = false;
+    bool force_radix = false;  // tests: take the device-wide radix paths even when the shared-memory fast paths apply
 
     // parameters + tables
     bool have_params = false;
@@ -97,6 +98,8 @@ struct kssd_ctx {
     kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
     uint64_t emit_cap = 0;
     kssd::DevBuf d_cursor;    // u64 cursor (+ spare words)
+    kssd::DevBuf d_gcount;    // u32 emitted keys per genome (written by the scan kernel)
+    kssd::DevBuf d_gcur, d_seg_start, d_ucount;  // per-genome scatter cursors, segment starts (u64), unique counts
     kssd::DevBuf d_stage_seq[2], d_stage_qual[2], d_stage_segoff[2], d_stage_seggen[2];
     cudaEvent_t stage_free[2] = {nullptr, nullptr};
     int stage_next = 0;
@@ -115,8 +118,9 @@ struct kssd_ctx {
     uint32_t n_ref = 0;
     uint32_t max_ref_size = 0;
     kssd::DevBuf d_uniq_hash, d_uniq_off, d_dict, d_ref_sizes, d_pairs, d_pairs_tmp;
-    kssd::DevBuf d_bucket;    // bucket_start[b] = first distinct hash with (hash >> bucket_shift) >= b; 2^16 + 1 entries
+    kssd::DevBuf d_bucket;    // bucket_start[b] = first distinct hash with (hash >> bucket_shift) >= b; n_buckets + 1 entries
     int bucket_shift = 0;
+    uint32_t n_buckets = 0;
     kssd::HostBuf h_uniq_hash, h_uniq_count, h_dict;
 
     // distances
@@ -138,12 +142,15 @@ int radix_sort_u64(kssd_ctx *c, uint64_t *d_keys, uint64_t *d_tmp, uint64_t n, i
                    int hi_bits_begin, int hi_bits_end, uint64_t **d_sorted);
 int unique_keys(kssd_ctx *c, const uint64_t *d_sorted, uint64_t n, int min_count, uint64_t *d_out_keys,
                 uint64_t *n_out);
+int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uint32_t max_count, int min_count,
+                       uint64_t *n_keep);   // segsort.cu: shared-memory per-genome sort + unique (fast path)
+int genome_segments(kssd_ctx *c);           // segsort.cu: gcount -> seg_start + max count (no sync)
 int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_genomes, uint32_t *d_hashes,
                   uint64_t *d_genome_off);
 // index.cu
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
                        uint64_t total);
-int index_build_buckets(kssd_ctx *c);  // after d_uniq_hash / n_uniq are in place
+int index_build_buckets(kssd_ctx *c, int64_t known_max_hash = -1);  // after d_uniq_hash / n_uniq are in place
 // dist.cu
 int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
                      uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,

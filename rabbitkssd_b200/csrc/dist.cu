@@ -17,48 +17,51 @@
 namespace kssd {
 
 // ---- step 1: per query hash, the posting range it has to stream --------------------------------------------
-__global__ void __launch_bounds__(256) list_lookup_kernel(const uint32_t *__restrict__ q_hashes, const uint64_t *__restrict__ q_off,
-                                                          uint32_t row_begin, uint32_t row_end, const uint32_t *__restrict__ uniq_hash,
-                                                          const uint64_t *__restrict__ uniq_off, uint64_t n_uniq,
-                                                          const uint32_t *__restrict__ bucket, int bucket_shift,
-                                                          const uint32_t *__restrict__ dict, int triangle,
-                                                          uint32_t *__restrict__ lb, uint32_t *__restrict__ le,
+// grid = (rows, chunks): the row is known from blockIdx.x, so nothing is searched but the hash itself (a coarse
+// directory narrows it to a handful of distinct hashes) and, for alldist, the first posting id > row.
+__global__ void __launch_bounds__(128) list_lookup_kernel(const uint32_t *__restrict__ q_hashes, const uint64_t *__restrict__ q_off,
+                                                          uint32_t row_begin, const uint32_t *__restrict__ uniq_hash,
+                                                          const uint64_t *__restrict__ uniq_off, const uint32_t *__restrict__ bucket,
+                                                          int bucket_shift, uint32_t n_buckets, const uint32_t *__restrict__ dict,
+                                                          int triangle, uint32_t *__restrict__ lb, uint32_t *__restrict__ le,
                                                           unsigned long long *__restrict__ posting_total) {
-    const uint64_t e0 = q_off[row_begin], e1 = q_off[row_end];
-    uint64_t e = e0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t len = 0;
-    if (e < e1) {
-        uint32_t h = q_hashes[e];
-        const uint32_t bk = min(h >> bucket_shift, 65535u);  // hashes above the largest indexed one fall into the last bucket
-        uint64_t lo = bucket[bk], hi = (h >> bucket_shift) > 65535u ? n_uniq : bucket[bk + 1];
-        while (lo < hi) {
-            uint64_t mid = (lo + hi) >> 1;
-            if (uniq_hash[mid] < h) lo = mid + 1; else hi = mid;
-        }
+    const uint32_t row = row_begin + blockIdx.x;
+    const uint64_t e_base = q_off[row_begin];
+    const uint64_t e0 = q_off[row], e1 = q_off[row + 1];
+    unsigned long long s = 0;
+    for (uint64_t e = e0 + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
+        const uint32_t h = q_hashes[e];
+        const uint32_t bk = h >> bucket_shift;
         uint32_t b = 0, en = 0;
-        if (lo < n_uniq && uniq_hash[lo] == h) {
-            b = (uint32_t)uniq_off[lo];
-            en = (uint32_t)uniq_off[lo + 1];
-            if (triangle) {
-                // owning row of element e, then first posting id > row (ids ascending inside a list)
-                uint32_t rlo = row_begin, rhi = row_end;
-                while (rhi - rlo > 1) {
-                    uint32_t mid = (rlo + rhi) >> 1;
-                    if (q_off[mid] <= e) rlo = mid; else rhi = mid;
+        if (bk < n_buckets) {  // hashes above the largest indexed one have no bucket
+            uint32_t lo = bucket[bk], hi = bucket[bk + 1];
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (uniq_hash[mid] < h) lo = mid + 1; else hi = mid;
+            }
+            if (lo < bucket[bk + 1] && uniq_hash[lo] == h) {
+                b = (uint32_t)uniq_off[lo];
+                en = (uint32_t)uniq_off[lo + 1];
+                if (triangle) {  // first posting id > row (ids ascending inside a list)
+                    if (en - b <= 8) {
+                        uint32_t skip = 0;
+                        for (uint32_t p = b; p < en; p++) skip += dict[p] <= row;  // independent loads
+                        b += skip;
+                    } else {
+                        uint32_t l2 = b, h2 = en;
+                        while (l2 < h2) {
+                            const uint32_t mid = (l2 + h2) >> 1;
+                            if (dict[mid] <= row) l2 = mid + 1; else h2 = mid;
+                        }
+                        b = l2;
+                    }
                 }
-                uint32_t l2 = b, h2 = en;
-                while (l2 < h2) {
-                    uint32_t mid = (l2 + h2) >> 1;
-                    if (dict[mid] <= rlo) l2 = mid + 1; else h2 = mid;
-                }
-                b = l2;
             }
         }
-        lb[e - e0] = b;
-        le[e - e0] = en;
-        len = en - b;
+        lb[e - e_base] = b;
+        le[e - e_base] = en;
+        s += en - b;
     }
-    unsigned long long s = len;
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
     if ((threadIdx.x & 31) == 0 && s) atomicAdd(posting_total, s);
 }
@@ -214,9 +217,13 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     unsigned long long *d_post_total = d_cursor + 1;
     KSSD_CUDA(cudaMemsetAsync(d_cursor, 0, 16, st));
     if (n_el) {
-        list_lookup_kernel<<<(unsigned)((n_el + 255) / 256), 256, 0, st>>>(
-            d_q_hashes, d_q_off, row_begin, row_end, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(), c->n_uniq,
-            c->d_bucket.as<uint32_t>(), c->bucket_shift, c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
+        // a row is cut into chunks only when rows are few and long (e.g. 20 mammal-size sketches of 46 k hashes)
+        const uint32_t n_rows_blk = row_end - row_begin;
+        const uint64_t avg_len = n_el / n_rows_blk + 1;
+        const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, std::min<uint64_t>(avg_len / 512, (4ull * c->sm_count * 16) / n_rows_blk)));
+        list_lookup_kernel<<<dim3(n_rows_blk, chunks), 128, 0, st>>>(
+            d_q_hashes, d_q_off, row_begin, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(),
+            c->d_bucket.as<uint32_t>(), c->bucket_shift, c->n_buckets, c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
         KSSD_CUDA(cudaGetLastError());
         c->launches++;
     }

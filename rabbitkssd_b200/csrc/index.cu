@@ -85,26 +85,24 @@ __global__ void __launch_bounds__(256) head_write_kernel(const uint64_t *__restr
 
 __global__ void set_u64_kernel(uint64_t *p, const uint64_t *idx, uint64_t v) { p[*idx] = v; }
 
-// Coarse directory over the sorted distinct hashes: a query hash is then found with ~5 binary-search steps inside
-// its bucket instead of ~21 over the whole array (list_lookup_kernel).
-static constexpr int kBucketBits = 16;
-__global__ void __launch_bounds__(256) bucket_start_kernel(const uint32_t *__restrict__ uniq_hash, uint64_t n_uniq, int shift,
-                                                           uint32_t *__restrict__ bucket) {
-    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b > (1u << kBucketBits)) return;
-    uint64_t lo = 0, hi = n_uniq;  // first u with (uniq_hash[u] >> shift) >= b
-    while (lo < hi) {
-        const uint64_t mid = (lo + hi) >> 1;
-        if ((uniq_hash[mid] >> shift) < b) lo = mid + 1; else hi = mid;
-    }
-    bucket[b] = (uint32_t)lo;
+// Coarse directory over the sorted distinct hashes: bucket[b] = first distinct hash u with (hash >> shift) >= b, so a
+// query hash is found with ~2 binary-search steps inside its bucket (list_lookup_kernel).  Built by one pass over
+// the distinct hashes: entry u fills the buckets between its predecessor's and its own.
+static constexpr int kBucketBits = 20;
+__global__ void __launch_bounds__(256) bucket_fill_kernel(const uint32_t *__restrict__ uniq_hash, uint32_t n_uniq, int shift,
+                                                          uint32_t n_buckets, uint32_t *__restrict__ bucket) {
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u > n_uniq) return;
+    const uint32_t lo = u == 0 ? 0 : (uniq_hash[u - 1] >> shift) + 1;
+    const uint32_t hi = u == n_uniq ? n_buckets : min(uniq_hash[u] >> shift, n_buckets);
+    for (uint32_t b = lo; b <= hi; b++) bucket[b] = u;
 }
 
-int index_build_buckets(kssd_ctx *c) {
+int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
     cudaStream_t st = c->stream;
-    KSSD_TRY(c->d_bucket.reserve(((1u << kBucketBits) + 1) * 4, st));
-    uint32_t mx = 0;
-    if (c->n_uniq) {
+    if (c->n_uniq >= (1ull << 32)) { set_error("index: more than 2^32 distinct hashes"); return KSSD_E_UNSUPPORTED; }
+    uint32_t mx = known_max_hash >= 0 ? (uint32_t)known_max_hash : 0;
+    if (c->n_uniq && known_max_hash < 0) {
         KSSD_TRY(c->h_scalar.reserve(64));
         KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, c->d_uniq_hash.as<uint32_t>() + (c->n_uniq - 1), 4, cudaMemcpyDeviceToHost, st));
         KSSD_CUDA(cudaStreamSynchronize(st));
@@ -113,10 +111,157 @@ int index_build_buckets(kssd_ctx *c) {
     int bits = 0;
     while (bits < 32 && (mx >> bits)) bits++;
     c->bucket_shift = bits > kBucketBits ? bits - kBucketBits : 0;
-    bucket_start_kernel<<<((1u << kBucketBits) + 1 + 255) / 256, 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), c->n_uniq, c->bucket_shift,
-                                                                              c->d_bucket.as<uint32_t>());
+    c->n_buckets = (mx >> c->bucket_shift) + 1;  // <= 2^kBucketBits
+    KSSD_TRY(c->d_bucket.reserve(((uint64_t)c->n_buckets + 1) * 4, st));
+    bucket_fill_kernel<<<(unsigned)((c->n_uniq + 1 + 255) / 256), 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), (uint32_t)c->n_uniq, c->bucket_shift,
+                                                                               c->n_buckets, c->d_bucket.as<uint32_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches++;
+    return KSSD_OK;
+}
+
+// ---- fast path: hash buckets sorted in shared memory ------------------------------------------------------------
+// (hash, genome) pairs are dealt into 2^B buckets by the top hash bits (histogram + cursors: two passes of global
+// atomics over the L2-resident bucket table), and every bucket (~1 k pairs) is sorted by ONE CTA in shared memory
+// on the full (hash << 32 | genome) key, which also gives the ascending genome ids inside a posting list
+// (the reference's push_back order, sketch.cpp:979-985).  ~50 B of HBM traffic per posting instead of the
+// 4 radix passes x 48 B of the device-wide sort below (kept for bucket overflow, i.e. heavily skewed hashes).
+static constexpr uint32_t kBucketCap = 8192;  // pairs per bucket: 64 KB of shared memory
+
+__global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, uint64_t total, int shift, uint32_t last_bucket,
+                                                          uint32_t *__restrict__ bcount) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < total) atomicAdd(bcount + min(hashes[i] >> shift, last_bucket), 1u);
+}
+
+// grid = (genomes, chunks): the genome id is blockIdx.x
+__global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
+                                                          uint32_t last_bucket, const uint64_t *__restrict__ bstart, uint32_t *__restrict__ bcur,
+                                                          uint64_t *__restrict__ pairs) {
+    const uint32_t g = blockIdx.x;
+    const uint64_t e1 = genome_off[g + 1];
+    for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
+        const uint32_t h = hashes[e];
+        const uint32_t b = min(h >> shift, last_bucket);
+        pairs[bstart[b] + atomicAdd(bcur + b, 1u)] = ((uint64_t)h << 32) | g;
+    }
+}
+
+// One CTA per bucket.  Writes the postings of the bucket (dict), its distinct hashes + list starts (compacted at the
+// head of the bucket's range of tmp_hash / tmp_rel), their number, and folds the largest hash into *max_hash.
+__global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart,
+                                                          uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash, uint32_t *__restrict__ tmp_rel,
+                                                          uint32_t *__restrict__ hcount, uint32_t *__restrict__ flags /* [0] overflow, [1] max hash */) {
+    extern __shared__ uint64_t s_pairs[];
+    __shared__ uint32_t warp_sums[8];
+    __shared__ uint32_t running;
+    const uint32_t b = blockIdx.x;
+    const uint64_t b0 = bstart[b];
+    const uint64_t n64 = bstart[b + 1] - b0;
+    if (n64 == 0 || n64 > kBucketCap) {
+        if (threadIdx.x == 0) {
+            hcount[b] = 0;
+            if (n64) atomicExch(flags, 1u);
+        }
+        return;
+    }
+    const uint32_t n = (uint32_t)n64;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_pairs[i] = pairs[b0 + i];
+    if (threadIdx.x == 0) running = 0;
+    __syncthreads();
+    bitonic_sort_smem<uint64_t>(s_pairs, n);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x) {
+        const uint32_t i = c0 + threadIdx.x;
+        bool head = false;
+        uint64_t v = 0;
+        if (i < n) {
+            v = s_pairs[i];
+            dict[b0 + i] = (uint32_t)v;
+            head = i == 0 || (uint32_t)(s_pairs[i - 1] >> 32) != (uint32_t)(v >> 32);
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, head);
+        if (lane == 0) warp_sums[w] = __popc(bal);
+        __syncthreads();
+        uint32_t wp = 0, tot = 0;
+        for (int q = 0; q < 8; q++) { const uint32_t x = warp_sums[q]; if (q < w) wp += x; tot += x; }
+        if (head) {
+            const uint64_t at = b0 + running + wp + __popc(bal & ((1u << lane) - 1));
+            tmp_hash[at] = (uint32_t)(v >> 32);
+            tmp_rel[at] = i;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) running += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        hcount[b] = running;
+        atomicMax(flags + 1, (uint32_t)(s_pairs[n - 1] >> 32));
+    }
+}
+
+__global__ void __launch_bounds__(128) bucket_pack_kernel(const uint64_t *__restrict__ bstart, const uint64_t *__restrict__ hstart,
+                                                          const uint32_t *__restrict__ tmp_hash, const uint32_t *__restrict__ tmp_rel,
+                                                          uint32_t n_buckets, uint64_t total, uint32_t *__restrict__ uniq_hash,
+                                                          uint64_t *__restrict__ uniq_off) {
+    const uint32_t b = blockIdx.x;
+    const uint64_t b0 = bstart[b], u0 = hstart[b];
+    const uint32_t n = (uint32_t)(hstart[b + 1] - u0);
+    for (uint32_t j = threadIdx.x; j < n; j += blockDim.x) {
+        uniq_hash[u0 + j] = tmp_hash[b0 + j];
+        uniq_off[u0 + j] = b0 + tmp_rel[b0 + j];
+    }
+    if (b == n_buckets - 1 && threadIdx.x == 0) uniq_off[hstart[n_buckets]] = total;
+}
+
+__global__ void segment_scan_kernel(const uint32_t *counts, uint32_t n, uint64_t *start, uint32_t *max_out);  // segsort.cu
+
+// Returns KSSD_OK with *done = false when a bucket overflowed (caller falls back to the radix path).
+static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total,
+                                int hash_bits, uint32_t *d_max_size, bool *done, uint64_t *n_uniq, uint32_t *max_hash) {
+    cudaStream_t st = c->stream;
+    *done = false;
+    int B = 0;
+    while (B < 18 && (total >> (B + 10)) > 0) B++;  // ~1 k pairs per bucket on average
+    if (B > hash_bits) B = hash_bits;
+    const int shift = hash_bits - B;
+    const uint32_t nb = 1u << B;
+    // scratch: [bstart nb+1][hstart nb+1] u64, then [bcount nb][bcur nb][hcount nb][flags 4] u32
+    KSSD_TRY(c->d_sort_counts.reserve(((uint64_t)nb + 1) * 16 + (uint64_t)nb * 12 + 16, st));
+    uint64_t *bstart = c->d_sort_counts.as<uint64_t>();
+    uint64_t *hstart = bstart + nb + 1;
+    uint32_t *bcount = reinterpret_cast<uint32_t *>(hstart + nb + 1);
+    uint32_t *bcur = bcount + nb, *hcount = bcur + nb, *flags = hcount + nb;
+    KSSD_CUDA(cudaMemsetAsync(bcount, 0, (uint64_t)nb * 12 + 16, st));
+    uint32_t *tmp_hash = c->d_pairs_tmp.as<uint32_t>();
+    uint32_t *tmp_rel = tmp_hash + total;
+    const uint64_t avg_len = total / n_genomes + 1;
+    const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, std::min<uint64_t>(avg_len / 512, (4ull * c->sm_count * 16) / n_genomes)));
+    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, bcount);
+    segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
+    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, bstart, bcur, c->d_pairs.as<uint64_t>());
+    static bool attr_done = false;
+    if (!attr_done) {
+        KSSD_CUDA(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBucketCap * 8)));
+        attr_done = true;
+    }
+    bucket_sort_kernel<<<nb, 256, kBucketCap * 8, st>>>(c->d_pairs.as<uint64_t>(), bstart, c->d_dict.as<uint32_t>(), tmp_hash, tmp_rel, hcount, flags);
+    segment_scan_kernel<<<1, 1024, 0, st>>>(hcount, nb, hstart, nullptr);
+    bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, total, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
+    KSSD_CUDA(cudaGetLastError());
+    c->launches += 6;
+    KSSD_TRY(c->h_scalar.reserve(64));
+    uint64_t *hs = c->h_scalar.as<uint64_t>();
+    KSSD_CUDA(cudaMemcpyAsync(hs, hstart + nb, 8, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaMemcpyAsync(hs + 1, flags, 8, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaMemcpyAsync(hs + 2, d_max_size, 4, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaStreamSynchronize(st));
+    const uint32_t *fl = reinterpret_cast<const uint32_t *>(hs + 1);
+    c->max_ref_size = *reinterpret_cast<const uint32_t *>(hs + 2);
+    if (fl[0]) return KSSD_OK;  // a bucket did not fit shared memory
+    *n_uniq = hs[0];
+    *max_hash = fl[1];
+    *done = true;
     return KSSD_OK;
 }
 
@@ -138,12 +283,21 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
     KSSD_TRY(c->d_uniq_hash.reserve(std::max<uint64_t>(total, 1) * 4, st));
     KSSD_TRY(c->d_uniq_off.reserve((total + 1) * 8, st));
     uint64_t n_uniq = 0;
-    if (total) {
+    int64_t known_max = -1;
+    bool done = false;
+    int hash_bits = c->have_params ? 4 * (c->sp.half_k - c->sp.drlevel) : 32;
+    if (hash_bits > 32) hash_bits = 32;
+    if (total && n_genomes && !c->force_radix && total < (1ull << 32)) {
+        uint32_t mh = 0;
+        KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, hash_bits, d_max, &done, &n_uniq, &mh));
+        if (done) known_max = mh;
+    }
+    if (done) {
+        // CSR is in place
+    } else if (total) {
         make_pairs_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, d_genome_off, n_genomes, total,
                                                                           c->d_pairs.as<uint64_t>());
         c->launches++;
-        int hash_bits = c->have_params ? 4 * (c->sp.half_k - c->sp.drlevel) : 32;
-        if (hash_bits > 32) hash_bits = 32;
         uint64_t *sorted = nullptr;
         KSSD_TRY(radix_sort_u64(c, c->d_pairs.as<uint64_t>(), c->d_pairs_tmp.as<uint64_t>(), total, 0, 0, 32, 32 + hash_bits, &sorted));
         uint32_t n_tiles = (uint32_t)((total + 4095) / 4096);
@@ -168,7 +322,7 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
         c->max_ref_size = 0;
     }
     c->n_uniq = n_uniq;
-    KSSD_TRY(index_build_buckets(c));
+    KSSD_TRY(index_build_buckets(c, known_max));
     c->have_index = true;
     return KSSD_OK;
 }

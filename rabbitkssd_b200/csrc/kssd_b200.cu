@@ -2,6 +2,7 @@
 // relocatable device code.  Build: see rabbitkssd_b200/build.py (nvcc -gencode arch=compute_100a,code=sm_100a).
 #include "sketch.cu"
 #include "radix.cu"
+#include "segsort.cu"
 #include "index.cu"
 #include "dist.cu"
 #include "capi.cu"

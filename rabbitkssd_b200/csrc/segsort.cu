@@ -1,0 +1,210 @@
+// Segment sort in shared memory: the fast path of "per-genome sort + unique" (and of the index build's buckets).
+//
+// Replaces the reference's per-genome unordered_set / unordered_map containers (src/sketch.cpp:526-550, :832-849,
+// count filter :704-706).  The scan kernel counts the keys it emits per genome, so the (genome, hash) keys can be
+// dealt into per-genome segments with one pass (warp-aggregated cursors) and every segment is then sorted by ONE
+// CTA entirely in shared memory (bitonic network, ascending-only variant so that a segment of any length sorts in
+// place without padding), deduplicated / count-filtered there and written back.  HBM traffic: 8 B + 4 B per key
+// for the deal, 4 B + 4 B for the sort, 4 B + 4 B for the final packing -- against 6 radix passes x 48 B per key
+// for the device-wide sort it replaces (radix.cu, still used when a segment does not fit shared memory).
+#include "common.cuh"
+
+namespace kssd {
+
+static constexpr uint32_t kSegSortMaxKeys = 56 * 1024;  // u32 keys: 224 KB of shared memory
+
+// Ascending-only bitonic network over s[0, n): every compare-exchange puts the smaller key at the lower index, so
+// the (virtual) +inf keys at indices >= n never move and need no storage.
+template <typename K>
+__device__ __forceinline__ void bitonic_sort_smem(K *s, uint32_t n) {
+    if (n < 2) return;
+    const uint32_t np = 1u << (32 - __clz(n - 1));  // next power of two >= n
+    const uint32_t half = np >> 1;
+    for (uint32_t k = 2; k <= np; k <<= 1) {
+        const uint32_t hk = k >> 1;
+        const int lg = 31 - __clz(hk);
+        for (uint32_t i = threadIdx.x; i < half; i += blockDim.x) {  // flip: i-th pair of its k-block is (off, k-1-off)
+            const uint32_t blk = i >> lg, off = i & (hk - 1);
+            const uint32_t a = blk * k + off, b = blk * k + (k - 1 - off);
+            if (b < n) {
+                const K x = s[a], y = s[b];
+                if (x > y) { s[a] = y; s[b] = x; }
+            }
+        }
+        __syncthreads();
+        for (uint32_t j = hk >> 1; j >= 1; j >>= 1) {
+            for (uint32_t i = threadIdx.x; i < half; i += blockDim.x) {
+                const uint32_t a = ((i & ~(j - 1)) << 1) | (i & (j - 1)), b = a + j;
+                if (b < n) {
+                    const K x = s[a], y = s[b];
+                    if (x > y) { s[a] = y; s[b] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// counts[n] -> start[n+1] (exclusive, 64-bit), *max_out = largest count.  Single CTA.
+__global__ void __launch_bounds__(1024) segment_scan_kernel(const uint32_t *__restrict__ counts, uint32_t n, uint64_t *__restrict__ start,
+                                                            uint32_t *__restrict__ max_out) {
+    __shared__ uint64_t warp_sums[32];
+    __shared__ uint32_t warp_max[32];
+    __shared__ uint64_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t mx = 0;
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint64_t v = i < n ? counts[i] : 0;
+        mx = max(mx, (uint32_t)v);
+        uint64_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sums[w] = x;
+        __syncthreads();
+        uint64_t wp = 0;
+        for (int q = 0; q < w; q++) wp += warp_sums[q];
+        const uint64_t excl = carry + wp + x - v;
+        if (i < n) start[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    if (lane == 0) warp_max[w] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        start[n] = carry;
+        uint32_t m = 0;
+        for (int q = 0; q < 32; q++) m = max(m, warp_max[q]);
+        if (max_out) *max_out = m;
+    }
+}
+
+// Deal the emitted (genome << 32 | hash) keys into per-genome segments.  Neighbouring keys mostly belong to the same
+// genome (a warp of the scan kernel appends its survivors together), so the cursor update is aggregated per warp.
+__global__ void __launch_bounds__(256) genome_deal_kernel(const uint64_t *__restrict__ emit, uint64_t n, const uint64_t *__restrict__ seg_start,
+                                                          uint32_t *__restrict__ gcur, uint32_t *__restrict__ seg) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool live = i < n;
+    const uint64_t key = live ? emit[i] : ~0ull;
+    const uint32_t g = (uint32_t)(key >> 32);
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, g);
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (live && lane == leader) base = atomicAdd(gcur + g, (uint32_t)__popc(peers));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (live) seg[seg_start[g] + base + __popc(peers & ((1u << lane) - 1))] = (uint32_t)key;
+}
+
+// One CTA per genome: sort the segment in shared memory, keep run heads whose run has >= min_count members
+// (min_count = 1: plain set, sketch.cpp:526-529; FASTQ -n: sketch.cpp:704-706), write them back to the head of the
+// segment and the number kept to ucount[genome].
+__global__ void __launch_bounds__(1024) genome_sort_unique_kernel(uint32_t *__restrict__ seg, const uint64_t *__restrict__ seg_start,
+                                                                  int min_count, uint32_t *__restrict__ ucount) {
+    extern __shared__ uint32_t s_keys[];
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t running;
+    const uint32_t g = blockIdx.x;
+    const uint64_t b0 = seg_start[g];
+    const uint32_t n = (uint32_t)(seg_start[g + 1] - b0);
+    uint32_t *base = seg + b0;
+    if (n == 0) {
+        if (threadIdx.x == 0) ucount[g] = 0;
+        return;
+    }
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = base[i];
+    if (threadIdx.x == 0) running = 0;
+    __syncthreads();
+    bitonic_sort_smem<uint32_t>(s_keys, n);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x) {
+        const uint32_t i = c0 + threadIdx.x;
+        bool kp = false;
+        uint32_t v = 0;
+        if (i < n) {
+            v = s_keys[i];
+            kp = i == 0 || s_keys[i - 1] != v;
+            if (kp && min_count > 1) {
+                const uint32_t j = i + (uint32_t)(min_count - 1);
+                kp = j < n && s_keys[j] == v;
+            }
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, kp);
+        if (lane == 0) warp_sums[w] = __popc(bal);
+        __syncthreads();
+        uint32_t wp = 0, tot = 0;
+        for (int q = 0; q < n_warps; q++) { const uint32_t x = warp_sums[q]; if (q < w) wp += x; tot += x; }
+        if (kp) base[running + wp + __popc(bal & ((1u << lane) - 1))] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) running += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) ucount[g] = running;
+}
+
+// Pack the kept heads of every segment into the final CSR (hashes, genome_off).
+__global__ void __launch_bounds__(128) genome_pack_kernel(const uint32_t *__restrict__ seg, const uint64_t *__restrict__ seg_start,
+                                                          const uint64_t *__restrict__ genome_off, uint32_t *__restrict__ hashes) {
+    const uint32_t g = blockIdx.x;
+    const uint64_t o0 = genome_off[g];
+    const uint32_t n = (uint32_t)(genome_off[g + 1] - o0);
+    const uint32_t *src = seg + seg_start[g];
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) hashes[o0 + i] = src[i];
+}
+
+// gcount -> seg_start (+ max count in d_cursor word 2); runs on the stream, no sync.
+int genome_segments(kssd_ctx *c) {
+    cudaStream_t st = c->stream;
+    KSSD_TRY(c->d_seg_start.reserve((uint64_t)(c->n_genomes + 1) * 8, st));
+    uint32_t *d_max = reinterpret_cast<uint32_t *>(c->d_cursor.as<unsigned long long>() + 2);
+    segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_gcount.as<uint32_t>(), c->n_genomes, c->d_seg_start.as<uint64_t>(), d_max);
+    KSSD_CUDA(cudaGetLastError());
+    c->launches++;
+    return KSSD_OK;
+}
+
+int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uint32_t max_count, int min_count, uint64_t *n_keep) {
+    cudaStream_t st = c->stream;
+    const uint32_t ng = c->n_genomes;
+    *n_keep = 0;
+    KSSD_TRY(c->d_gcur.reserve((uint64_t)std::max<uint32_t>(ng, 1) * 4, st));
+    KSSD_TRY(c->d_ucount.reserve((uint64_t)std::max<uint32_t>(ng, 1) * 4, st));
+    KSSD_TRY(c->d_sort_tmp.reserve(std::max<uint64_t>(n_emit, 1) * 4, st));
+    KSSD_TRY(c->d_hashes.reserve(std::max<uint64_t>(n_emit, 1) * 4, st));
+    KSSD_TRY(c->d_genome_off.reserve((uint64_t)(ng + 1) * 8, st));
+    if (ng == 0) return KSSD_OK;
+    uint32_t *seg = c->d_sort_tmp.as<uint32_t>();
+    uint64_t *seg_start = c->d_seg_start.as<uint64_t>();
+    KSSD_CUDA(cudaMemsetAsync(c->d_gcur.p, 0, (uint64_t)ng * 4, st));
+    if (n_emit) {
+        genome_deal_kernel<<<(unsigned)((n_emit + 255) / 256), 256, 0, st>>>(d_emit, n_emit, seg_start, c->d_gcur.as<uint32_t>(), seg);
+        c->launches++;
+    }
+    static bool attr_done = false;
+    if (!attr_done) {
+        KSSD_CUDA(cudaFuncSetAttribute(genome_sort_unique_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSegSortMaxKeys * 4)));
+        attr_done = true;
+    }
+    const int threads = max_count <= 2048 ? 256 : max_count <= 8192 ? 512 : 1024;
+    const size_t smem = (size_t)std::max<uint32_t>(max_count, 1) * 4;
+    genome_sort_unique_kernel<<<ng, threads, smem, st>>>(seg, seg_start, min_count, c->d_ucount.as<uint32_t>());
+    uint64_t *goff = c->d_genome_off.as<uint64_t>();
+    segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_ucount.as<uint32_t>(), ng, goff, nullptr);
+    genome_pack_kernel<<<ng, 128, 0, st>>>(seg, seg_start, goff, c->d_hashes.as<uint32_t>());
+    KSSD_CUDA(cudaGetLastError());
+    c->launches += 3;
+    KSSD_TRY(c->h_scalar.reserve(64));
+    KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, goff + ng, 8, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaStreamSynchronize(st));
+    *n_keep = *c->h_scalar.as<uint64_t>();
+    return KSSD_OK;
+}
+
+}  // namespace kssd

@@ -47,6 +47,8 @@ struct ScanArgs {
     uint32_t n_seg;
     uint64_t pos_base;
     unsigned long long *cursor;
+    uint32_t *gcount;          // emitted keys per genome (sizes the per-genome segments of the shared-memory sort)
+    uint32_t n_genomes;
     uint64_t emit_cap;
     uint32_t n_tiles;
     uint32_t n_interior;       // tiles [1, n_interior) lie completely inside the buffer (halo included)
@@ -329,7 +331,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
                     const uint32_t mid = (lo + hi) >> 1;
                     if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
                 }
-                a.emit[at] = ((unsigned long long)__ldg(a.seg_genome + lo) << 32) | hash;
+                const uint32_t genome = __ldg(a.seg_genome + lo);
+                a.emit[at] = ((unsigned long long)genome << 32) | hash;
+                if (genome < a.n_genomes) atomicAdd(a.gcount + genome, 1u);  // emits are rare (one per ~16^l bases): no aggregation needed
             }
         }
     };
@@ -560,6 +564,8 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.seg_genome = d_seg_genome;
     a.n_seg = n_seg;
     a.cursor = c->d_cursor.as<unsigned long long>();
+    a.gcount = c->d_gcount.as<uint32_t>();
+    a.n_genomes = c->n_genomes;
     a.emit_cap = c->emit_cap;
     a.sp = sp;
     a.bitmap_words = (uint32_t)std::max<uint64_t>((1ull << (2 * sp.nb)) / 32, 4);

@@ -11,9 +11,12 @@ pytestmark = pytest.mark.gpu
 CASES = sorted(util.golden_meta().keys())
 
 
-@pytest.fixture(scope="module")
-def ctx():
+# every test runs on both implementations of the sorts: the shared-memory segment sorts (default) and the
+# device-wide radix sort they fall back to
+@pytest.fixture(scope="module", params=["segsort", "radix"])
+def ctx(request):
     c = api.Context(0)
+    c.set_force_radix(request.param == "radix")
     yield c
     c.close()
 
@@ -182,3 +185,36 @@ def test_full_size_properties_c1(ctx):
     sets2, _, _ = _gpu_sketch(ctx, k, s, l, fam[:4])
     for a, b in zip(sets[:4], sets2):
         assert np.array_equal(a, b)
+
+
+def test_sort_fallbacks_when_shared_memory_is_too_small():
+    """A genome with more emitted keys than one CTA's shared memory holds (> 57,344) takes the radix path on its own;
+    an index whose hashes crowd one bucket (> 8,192 pairs) does too.  Both must equal the oracle."""
+    c = api.Context(0)
+    try:
+        k, s, l = 8, 5, 2
+        g = [[synth.random_bases(8181, 16000000)], [synth.random_bases(8182, 200000)]]
+        c.set_params(k, s, l, util.shuffled_dim(k, s, l))
+        seq, qual, off = synth.pack_batch(g)
+        h, goff = c.sketch(seq, off)
+        assert goff[1] > 57344
+        want = util.oracle_sketch(k, s, l, g)
+        for i in range(2):
+            assert np.array_equal(h[int(goff[i]):int(goff[i + 1])].astype(np.uint64), want[i]), i
+        rng = np.random.default_rng(5)
+        sets = [np.unique(rng.integers(0, 4096, 400)).astype(np.uint64) for _ in range(40)]
+        sh, soff = util.flatten_sets(sets)
+        assert soff[-1] > 8192
+        c.index_build(sh, soff)
+        uh, uc, dict_ = c.index_export()
+        o_dict, o_uh, o_uc, _ = oracle.index_build(sh, soff)
+        assert np.array_equal(dict_, o_dict)
+        sizes = np.diff(soff).astype(np.int64)
+        hits = c.dist_rows(sh, soff, True, 16, 0.3)
+        hits, _, _ = api.refine_hits(hits, sizes, sizes, 16, 0.3, True)
+        hr, hc, hm = oracle.alldist(sh, soff, 16, 0.3)
+        o = np.lexsort((hits[:, 1], hits[:, 0]))
+        assert len(hr) > 10
+        assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
+    finally:
+        c.close()
