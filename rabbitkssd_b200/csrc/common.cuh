@@ -96,10 +96,11 @@ struct kssd_ctx {
     int has_qual = 0, least_qual = 0, least_num_kmer = 1;
     uint64_t bases_submitted = 0;
     kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
+    kssd::DevBuf d_emit_rank; // u32 rank of each key inside its genome
     uint64_t emit_cap = 0;
     kssd::DevBuf d_cursor;    // u64 cursor (+ spare words)
     kssd::DevBuf d_gcount;    // u32 emitted keys per genome (written by the scan kernel)
-    kssd::DevBuf d_gcur, d_seg_start, d_ucount;  // per-genome scatter cursors, segment starts (u64), unique counts
+    kssd::DevBuf d_seg_start, d_ucount;  // per-genome segment starts (u64), unique counts
     kssd::DevBuf d_stage_seq[2], d_stage_qual[2], d_stage_segoff[2], d_stage_seggen[2];
     cudaEvent_t stage_free[2] = {nullptr, nullptr};
     int stage_next = 0;

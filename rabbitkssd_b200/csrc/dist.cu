@@ -67,6 +67,8 @@ __global__ void __launch_bounds__(128) list_lookup_kernel(const uint32_t *__rest
 }
 
 // ---- step 2: count + epilogue -------------------------------------------------------------------------------
+static constexpr uint32_t kListCap = 4096;  // cells per epilogue chunk = 512 threads x 8 (16-bit) cells
+
 struct DistArgs {
     const uint64_t *q_off;
     const uint32_t *lb, *le;
@@ -80,6 +82,7 @@ struct DistArgs {
     int triangle;
     int containment;
     int zero_pass;          // cells with common == 0 (or an empty sketch) pass the threshold
+    uint32_t list_word_off; // word offset of the non-zero-cell list behind the counters in shared memory
     double neg_inv_k;       // -1.0 / kmer_size
     double dist_limit;      // conservative upper bound on the distance
     kssd_hit *hits;
@@ -151,9 +154,77 @@ __global__ void __launch_bounds__(512) dist_tile_kernel(const DistArgs a) {
     __syncthreads();
 
     // epilogue: scan the tile, distance + threshold, compacted output
-    for (uint32_t r = 0; r < n_rows; r++) {
-        const uint32_t row = r0 + r;
+    auto evaluate = [&](uint32_t row, uint32_t j, uint32_t c) -> bool {  // conservative device-side threshold test
         const uint32_t size_q = (uint32_t)(a.q_off[row + 1] - a.q_off[row]);
+        const uint32_t size_r = a.ref_sizes[j];
+        double v;  // jaccard or containment
+        if (!a.containment) v = (double)c / (double)(int)(size_q + size_r - c);
+        else v = (double)c / (double)min(size_q, size_r);
+        double d;
+        if (v == 1.0) d = 0.0;
+        else if (!a.containment) d = a.neg_inv_k * log((2 * v) / (1.0 + v));
+        else d = a.neg_inv_k * log(v);
+        return d <= a.dist_limit;
+    };
+    auto append = [&](bool pass, uint32_t row, uint32_t j, uint32_t c) {  // warp-aggregated; all 32 lanes call it
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, pass);
+        if (bal) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(a.hit_cursor, (unsigned long long)__popc(bal));
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (pass) {
+                const unsigned long long at = base + __popc(bal & ((1u << lane) - 1));
+                if (at < a.hit_cap) { kssd_hit h; h.row = row; h.col = j; h.common = c; a.hits[at] = h; }
+            }
+        }
+    };
+    if (!a.zero_pass) {
+        // Almost every cell is zero: read the counters 16 bytes at a time, collect the non-zero cells of a chunk in a
+        // shared-memory list (a cell is non-zero only if a posting with a legal column id was counted into it), then
+        // evaluate the listed cells.  A chunk has at most kListCap cells, so the list cannot overflow.
+        constexpr uint32_t V = 16 / sizeof(CNT);
+        uint32_t *list = reinterpret_cast<uint32_t *>(s_raw) + a.list_word_off;
+        __shared__ uint32_t list_n;
+        if (threadIdx.x == 0) list_n = 0;
+        __syncthreads();
+        const uint32_t n_vec = (n_rows * tc) / V;  // tc is a multiple of 8
+        for (uint32_t vb = 0; vb < n_vec; vb += blockDim.x) {
+            const uint32_t v = vb + threadIdx.x;
+            if (v < n_vec) {
+                const uint4 q = s_raw[v];
+                if (q.x | q.y | q.z | q.w) {
+                    const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                    for (uint32_t k = 0; k < V; k++) {
+                        const uint32_t cval = sizeof(CNT) == 2 ? (w4[k >> 1] >> (16 * (k & 1))) & 0xFFFFu : w4[k & 3];
+                        if (cval) list[atomicAdd(&list_n, 1u)] = v * V + k;
+                    }
+                }
+            }
+            __syncthreads();
+            const uint32_t n_list = list_n;
+            for (uint32_t t = threadIdx.x; t < ((n_list + 31) & ~31u); t += blockDim.x) {
+                bool pass = false;
+                uint32_t row = 0, j = 0, c = 0;
+                if (t < n_list) {
+                    const uint32_t ci = list[t];
+                    const uint32_t r = ci / tc;
+                    row = r0 + r;
+                    j = c0 + (ci - r * tc);
+                    c = cnt[ci];
+                    pass = evaluate(row, j, c);
+                }
+                append(pass, row, j, c);
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) list_n = 0;
+            // the next chunk's atomics come after its own __syncthreads-free region: make the reset visible first
+            __syncthreads();
+        }
+        return;
+    }
+    for (uint32_t r = 0; r < n_rows; r++) {  // every zero cell passes too: dense output
+        const uint32_t row = r0 + r;
         const CNT *row_cnt = cnt + (uint64_t)r * tc;
         uint32_t jstart = c0;
         if (a.triangle && row + 1 > jstart) jstart = row + 1;
@@ -164,30 +235,9 @@ __global__ void __launch_bounds__(512) dist_tile_kernel(const DistArgs a) {
             uint32_t j = jstart + t, c = 0;
             if (t < span) {
                 c = row_cnt[j - c0];
-                if (c == 0) {
-                    pass = a.zero_pass;
-                } else {
-                    uint32_t size_r = a.ref_sizes[j];
-                    double v;  // jaccard or containment
-                    if (!a.containment) v = (double)c / (double)(int)(size_q + size_r - c);
-                    else v = (double)c / (double)min(size_q, size_r);
-                    double d;
-                    if (v == 1.0) d = 0.0;
-                    else if (!a.containment) d = a.neg_inv_k * log((2 * v) / (1.0 + v));
-                    else d = a.neg_inv_k * log(v);
-                    pass = d <= a.dist_limit;
-                }
+                pass = c == 0 ? true : evaluate(row, j, c);
             }
-            uint32_t bal = __ballot_sync(0xFFFFFFFFu, pass);
-            if (bal) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(a.hit_cursor, (unsigned long long)__popc(bal));
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (pass) {
-                    unsigned long long at = base + __popc(bal & ((1u << lane) - 1));
-                    if (at < a.hit_cap) { kssd_hit h; h.row = row; h.col = j; h.common = c; a.hits[at] = h; }
-                }
-            }
+            append(pass, row, j, c);
         }
     }
 }
@@ -217,10 +267,9 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     unsigned long long *d_post_total = d_cursor + 1;
     KSSD_CUDA(cudaMemsetAsync(d_cursor, 0, 16, st));
     if (n_el) {
-        // a row is cut into chunks only when rows are few and long (e.g. 20 mammal-size sketches of 46 k hashes)
         const uint32_t n_rows_blk = row_end - row_begin;
         const uint64_t avg_len = n_el / n_rows_blk + 1;
-        const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, std::min<uint64_t>(avg_len / 512, (4ull * c->sm_count * 16) / n_rows_blk)));
+        const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);  // ~2 hashes per thread
         list_lookup_kernel<<<dim3(n_rows_blk, chunks), 128, 0, st>>>(
             d_q_hashes, d_q_off, row_begin, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(),
             c->d_bucket.as<uint32_t>(), c->bucket_shift, c->n_buckets, c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
@@ -245,7 +294,8 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     uint32_t tq_fill = std::max<uint32_t>(1, rows / want_tiles);
     tq = std::min(tq, tq_fill);
     const uint32_t n_row_tiles = (rows + tq - 1) / tq;
-    const size_t smem = (size_t)tq * tc * cnt_bytes;
+    const size_t cnt_smem = ((size_t)tq * tc * cnt_bytes + 15) & ~(size_t)15;
+    const size_t smem = cnt_smem + kListCap * 4;
 
     DistArgs a;
     a.q_off = d_q_off;
@@ -267,11 +317,12 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     a.neg_inv_k = -1.0 / kmer_size;
     a.dist_limit = max_dist + std::fabs(max_dist) * 1e-9 + 1e-12;
     a.hit_cursor = d_cursor;
+    a.list_word_off = (uint32_t)(cnt_smem / 4);
 
     static bool attr_done = false;
     if (!attr_done) {
-        KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+        KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
         attr_done = true;
     }
     uint64_t hit_cap = c->d_hits.cap / sizeof(kssd_hit);

@@ -126,7 +126,8 @@ int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
 // on the full (hash << 32 | genome) key, which also gives the ascending genome ids inside a posting list
 // (the reference's push_back order, sketch.cpp:979-985).  ~50 B of HBM traffic per posting instead of the
 // 4 radix passes x 48 B of the device-wide sort below (kept for bucket overflow, i.e. heavily skewed hashes).
-static constexpr uint32_t kBucketCap = 8192;  // pairs per bucket: 64 KB of shared memory
+static constexpr uint32_t kBucketCapSmall = 2048, kBucketCapLarge = 8192;  // pairs per bucket: 16 KB / 64 KB of shared memory
+static constexpr uint32_t kSubBuckets = 1024;                               // counting-sort buckets inside a bucket
 
 __global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, uint64_t total, int shift, uint32_t last_bucket,
                                                           uint32_t *__restrict__ bcount) {
@@ -149,16 +150,17 @@ __global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__rest
 
 // One CTA per bucket.  Writes the postings of the bucket (dict), its distinct hashes + list starts (compacted at the
 // head of the bucket's range of tmp_hash / tmp_rel), their number, and folds the largest hash into *max_hash.
-__global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart,
-                                                          uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash, uint32_t *__restrict__ tmp_rel,
-                                                          uint32_t *__restrict__ hcount, uint32_t *__restrict__ flags /* [0] overflow, [1] max hash */) {
+__global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart, int shift,
+                                                          uint32_t cap, uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash,
+                                                          uint32_t *__restrict__ tmp_rel, uint32_t *__restrict__ hcount,
+                                                          uint32_t *__restrict__ flags /* [0] overflow, [1] max hash */) {
     extern __shared__ uint64_t s_pairs[];
     __shared__ uint32_t warp_sums[8];
     __shared__ uint32_t running;
     const uint32_t b = blockIdx.x;
     const uint64_t b0 = bstart[b];
     const uint64_t n64 = bstart[b + 1] - b0;
-    if (n64 == 0 || n64 > kBucketCap) {
+    if (n64 == 0 || n64 > cap) {
         if (threadIdx.x == 0) {
             hcount[b] = 0;
             if (n64) atomicExch(flags, 1u);
@@ -166,10 +168,13 @@ __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__rest
         return;
     }
     const uint32_t n = (uint32_t)n64;
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_pairs[i] = pairs[b0 + i];
     if (threadIdx.x == 0) running = 0;
-    __syncthreads();
-    bitonic_sort_smem<uint64_t>(s_pairs, n);
+    {   // sub-bucket = the hash bits below the bucket prefix (clamped: the last bucket also holds out-of-range hashes)
+        const int sub_shift = shift > 10 ? shift - 10 : 0;
+        const uint32_t first = (uint32_t)(((uint64_t)b << shift) >> sub_shift);
+        count_sort_smem<uint64_t>(pairs + b0, s_pairs, reinterpret_cast<uint32_t *>(s_pairs + cap), n, kSubBuckets,
+                                  [=](uint64_t k) { return min(((uint32_t)(k >> 32) >> sub_shift) - first, kSubBuckets - 1); });
+    }
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x) {
         const uint32_t i = c0 + threadIdx.x;
@@ -240,25 +245,33 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, bcount);
     segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
     bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, bstart, bcur, c->d_pairs.as<uint64_t>());
+    KSSD_CUDA(cudaGetLastError());
+    c->launches += 3;
     static bool attr_done = false;
     if (!attr_done) {
-        KSSD_CUDA(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBucketCap * 8)));
+        KSSD_CUDA(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBucketCapLarge * 8 + kSubBuckets * 4)));
         attr_done = true;
     }
-    bucket_sort_kernel<<<nb, 256, kBucketCap * 8, st>>>(c->d_pairs.as<uint64_t>(), bstart, c->d_dict.as<uint32_t>(), tmp_hash, tmp_rel, hcount, flags);
-    segment_scan_kernel<<<1, 1024, 0, st>>>(hcount, nb, hstart, nullptr);
-    bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, total, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
-    KSSD_CUDA(cudaGetLastError());
-    c->launches += 6;
     KSSD_TRY(c->h_scalar.reserve(64));
     uint64_t *hs = c->h_scalar.as<uint64_t>();
-    KSSD_CUDA(cudaMemcpyAsync(hs, hstart + nb, 8, cudaMemcpyDeviceToHost, st));
-    KSSD_CUDA(cudaMemcpyAsync(hs + 1, flags, 8, cudaMemcpyDeviceToHost, st));
-    KSSD_CUDA(cudaMemcpyAsync(hs + 2, d_max_size, 4, cudaMemcpyDeviceToHost, st));
-    KSSD_CUDA(cudaStreamSynchronize(st));
     const uint32_t *fl = reinterpret_cast<const uint32_t *>(hs + 1);
-    c->max_ref_size = *reinterpret_cast<const uint32_t *>(hs + 2);
-    if (fl[0]) return KSSD_OK;  // a bucket did not fit shared memory
+    // small shared-memory footprint first (more CTAs per SM); one retry with the large one when a bucket overflowed
+    for (uint32_t cap : {kBucketCapSmall, kBucketCapLarge}) {
+        KSSD_CUDA(cudaMemsetAsync(flags, 0, 16, st));
+        bucket_sort_kernel<<<nb, 256, (size_t)cap * 8 + kSubBuckets * 4, st>>>(c->d_pairs.as<uint64_t>(), bstart, shift, cap, c->d_dict.as<uint32_t>(),
+                                                                               tmp_hash, tmp_rel, hcount, flags);
+        segment_scan_kernel<<<1, 1024, 0, st>>>(hcount, nb, hstart, nullptr);
+        bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, total, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
+        KSSD_CUDA(cudaGetLastError());
+        c->launches += 3;
+        KSSD_CUDA(cudaMemcpyAsync(hs, hstart + nb, 8, cudaMemcpyDeviceToHost, st));
+        KSSD_CUDA(cudaMemcpyAsync(hs + 1, flags, 8, cudaMemcpyDeviceToHost, st));
+        KSSD_CUDA(cudaMemcpyAsync(hs + 2, d_max_size, 4, cudaMemcpyDeviceToHost, st));
+        KSSD_CUDA(cudaStreamSynchronize(st));
+        c->max_ref_size = *reinterpret_cast<const uint32_t *>(hs + 2);
+        if (!fl[0]) break;
+    }
+    if (fl[0]) return KSSD_OK;  // a bucket does not fit shared memory: caller takes the radix path
     *n_uniq = hs[0];
     *max_hash = fl[1];
     *done = true;

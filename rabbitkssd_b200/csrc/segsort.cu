@@ -2,9 +2,9 @@
 //
 // Replaces the reference's per-genome unordered_set / unordered_map containers (src/sketch.cpp:526-550, :832-849,
 // count filter :704-706).  The scan kernel counts the keys it emits per genome, so the (genome, hash) keys can be
-// dealt into per-genome segments with one pass (warp-aggregated cursors) and every segment is then sorted by ONE
-// CTA entirely in shared memory (bitonic network, ascending-only variant so that a segment of any length sorts in
-// place without padding), deduplicated / count-filtered there and written back.  HBM traffic: 8 B + 4 B per key
+// dealt into per-genome segments with one pass (the scan kernel also records each key's rank inside its genome) and
+// every segment is then sorted by ONE CTA entirely in shared memory (counting-bucket sort on the leading hash bits;
+// bitonic network as fallback), deduplicated / count-filtered there and written back.  HBM traffic: 8 B + 4 B per key
 // for the deal, 4 B + 4 B for the sort, 4 B + 4 B for the final packing -- against 6 radix passes x 48 B per key
 // for the device-wide sort it replaces (radix.cu, still used when a segment does not fit shared memory).
 #include "common.cuh"
@@ -43,6 +43,66 @@ __device__ __forceinline__ void bitonic_sort_smem(K *s, uint32_t n) {
             __syncthreads();
         }
     }
+}
+
+// Counting-bucket sort of n keys from global memory into shared memory: hashes are uniform, so NB >= n/4 buckets on
+// the leading key bits hold a handful of keys each -- one shared-memory atomic to count, one to place, and a
+// per-thread insertion sort of each tiny bucket, instead of the ~log^2(n)/2 compare-exchange rounds of the bitonic
+// network (which remains the fallback when some bucket is crowded, e.g. one hash shared by a thousand genomes).
+// bucket(key) must be non-decreasing in key and < NB.  cnt: NB counters.  On return dst[0, n) is sorted.
+template <typename K, typename F>
+__device__ __forceinline__ void count_sort_smem(const K *src, K *dst, uint32_t *cnt, uint32_t n, uint32_t NB, F bucket) {
+    __shared__ uint32_t cs_warp[32];
+    __shared__ uint32_t cs_carry, cs_max;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    for (uint32_t i = threadIdx.x; i < NB; i += blockDim.x) cnt[i] = 0;
+    if (threadIdx.x == 0) { cs_carry = 0; cs_max = 0; }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(cnt + bucket(src[i]), 1u);
+    __syncthreads();
+    uint32_t mx = 0;
+    for (uint32_t base = 0; base < NB; base += blockDim.x) {  // exclusive scan of the counters, in place
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < NB ? cnt[i] : 0;
+        mx = max(mx, v);
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) cs_warp[w] = x;
+        __syncthreads();
+        uint32_t wp = 0, tot = 0;
+        for (int q = 0; q < n_warps; q++) { const uint32_t t = cs_warp[q]; if (q < w) wp += t; tot += t; }
+        if (i < NB) cnt[i] = cs_carry + wp + x - v;
+        __syncthreads();
+        if (threadIdx.x == 0) cs_carry += tot;
+    }
+    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    if (lane == 0 && mx) atomicMax(&cs_max, mx);
+    __syncthreads();
+    if (cs_max > 32) {  // crowded bucket: sort the whole segment with the network instead
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+        __syncthreads();
+        bitonic_sort_smem<K>(dst, n);
+        return;
+    }
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const K k = src[i];
+        dst[atomicAdd(cnt + bucket(k), 1u)] = k;
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < NB; b += blockDim.x) {  // cnt[b] is now the END of bucket b
+        const uint32_t beg = b ? cnt[b - 1] : 0, end = cnt[b];
+        for (uint32_t i = beg + 1; i < end; i++) {
+            const K k = dst[i];
+            uint32_t j = i;
+            while (j > beg && dst[j - 1] > k) { dst[j] = dst[j - 1]; j--; }
+            dst[j] = k;
+        }
+    }
+    __syncthreads();
 }
 
 // counts[n] -> start[n+1] (exclusive, 64-bit), *max_out = largest count.  Single CTA.
@@ -86,28 +146,23 @@ __global__ void __launch_bounds__(1024) segment_scan_kernel(const uint32_t *__re
     }
 }
 
-// Deal the emitted (genome << 32 | hash) keys into per-genome segments.  Neighbouring keys mostly belong to the same
-// genome (a warp of the scan kernel appends its survivors together), so the cursor update is aggregated per warp.
-__global__ void __launch_bounds__(256) genome_deal_kernel(const uint64_t *__restrict__ emit, uint64_t n, const uint64_t *__restrict__ seg_start,
-                                                          uint32_t *__restrict__ gcur, uint32_t *__restrict__ seg) {
+// Deal the emitted (genome << 32 | hash) keys into per-genome segments: the scan kernel recorded the rank of every key
+// inside its genome, so this is a plain permutation (no atomics).
+__global__ void __launch_bounds__(256) genome_deal_kernel(const uint64_t *__restrict__ emit, const uint32_t *__restrict__ emit_rank, uint64_t n,
+                                                          uint32_t n_genomes, const uint64_t *__restrict__ seg_start, uint32_t *__restrict__ seg) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
-    const bool live = i < n;
-    const uint64_t key = live ? emit[i] : ~0ull;
+    if (i >= n) return;
+    const uint64_t key = emit[i];
     const uint32_t g = (uint32_t)(key >> 32);
-    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, g);
-    const int leader = __ffs(peers) - 1;
-    uint32_t base = 0;
-    if (live && lane == leader) base = atomicAdd(gcur + g, (uint32_t)__popc(peers));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    if (live) seg[seg_start[g] + base + __popc(peers & ((1u << lane) - 1))] = (uint32_t)key;
+    if (g < n_genomes) seg[seg_start[g] + emit_rank[i]] = (uint32_t)key;
 }
 
 // One CTA per genome: sort the segment in shared memory, keep run heads whose run has >= min_count members
 // (min_count = 1: plain set, sketch.cpp:526-529; FASTQ -n: sketch.cpp:704-706), write them back to the head of the
 // segment and the number kept to ucount[genome].
 __global__ void __launch_bounds__(1024) genome_sort_unique_kernel(uint32_t *__restrict__ seg, const uint64_t *__restrict__ seg_start,
-                                                                  int min_count, uint32_t *__restrict__ ucount) {
+                                                                  int min_count, uint32_t n_buckets /* 0: bitonic only */, int bucket_shift,
+                                                                  uint32_t key_cap, uint32_t *__restrict__ ucount) {
     extern __shared__ uint32_t s_keys[];
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t running;
@@ -119,10 +174,15 @@ __global__ void __launch_bounds__(1024) genome_sort_unique_kernel(uint32_t *__re
         if (threadIdx.x == 0) ucount[g] = 0;
         return;
     }
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = base[i];
     if (threadIdx.x == 0) running = 0;
-    __syncthreads();
-    bitonic_sort_smem<uint32_t>(s_keys, n);
+    if (n_buckets) {
+        const uint32_t last = n_buckets - 1;
+        count_sort_smem<uint32_t>(base, s_keys, s_keys + key_cap, n, n_buckets, [=](uint32_t h) { return min(h >> bucket_shift, last); });
+    } else {
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = base[i];
+        __syncthreads();
+        bitonic_sort_smem<uint32_t>(s_keys, n);
+    }
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x) {
         const uint32_t i = c0 + threadIdx.x;
@@ -174,7 +234,6 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
     cudaStream_t st = c->stream;
     const uint32_t ng = c->n_genomes;
     *n_keep = 0;
-    KSSD_TRY(c->d_gcur.reserve((uint64_t)std::max<uint32_t>(ng, 1) * 4, st));
     KSSD_TRY(c->d_ucount.reserve((uint64_t)std::max<uint32_t>(ng, 1) * 4, st));
     KSSD_TRY(c->d_sort_tmp.reserve(std::max<uint64_t>(n_emit, 1) * 4, st));
     KSSD_TRY(c->d_hashes.reserve(std::max<uint64_t>(n_emit, 1) * 4, st));
@@ -182,9 +241,8 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
     if (ng == 0) return KSSD_OK;
     uint32_t *seg = c->d_sort_tmp.as<uint32_t>();
     uint64_t *seg_start = c->d_seg_start.as<uint64_t>();
-    KSSD_CUDA(cudaMemsetAsync(c->d_gcur.p, 0, (uint64_t)ng * 4, st));
     if (n_emit) {
-        genome_deal_kernel<<<(unsigned)((n_emit + 255) / 256), 256, 0, st>>>(d_emit, n_emit, seg_start, c->d_gcur.as<uint32_t>(), seg);
+        genome_deal_kernel<<<(unsigned)((n_emit + 255) / 256), 256, 0, st>>>(d_emit, c->d_emit_rank.as<uint32_t>(), n_emit, ng, seg_start, seg);
         c->launches++;
     }
     static bool attr_done = false;
@@ -193,8 +251,20 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
         attr_done = true;
     }
     const int threads = max_count <= 2048 ? 256 : max_count <= 8192 ? 512 : 1024;
-    const size_t smem = (size_t)std::max<uint32_t>(max_count, 1) * 4;
-    genome_sort_unique_kernel<<<ng, threads, smem, st>>>(seg, seg_start, min_count, c->d_ucount.as<uint32_t>());
+    const uint32_t key_cap = std::max<uint32_t>(max_count, 1);
+    // counting-bucket sort while keys + counters fit (<= 32 k keys); the largest segments use the network alone
+    uint32_t nb = 0;
+    int shift = 0;
+    if (max_count <= 32768) {
+        nb = 32;
+        while (nb < max_count && nb < 8192) nb <<= 1;
+        int lg = 0;
+        while ((1u << lg) < nb) lg++;
+        const int hash_bits = std::min(32, 4 * (c->sp.half_k - c->sp.drlevel));
+        shift = std::max(0, hash_bits - lg);
+    }
+    const size_t smem = ((size_t)key_cap + nb) * 4;
+    genome_sort_unique_kernel<<<ng, threads, smem, st>>>(seg, seg_start, min_count, nb, shift, key_cap, c->d_ucount.as<uint32_t>());
     uint64_t *goff = c->d_genome_off.as<uint64_t>();
     segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_ucount.as<uint32_t>(), ng, goff, nullptr);
     genome_pack_kernel<<<ng, 128, 0, st>>>(seg, seg_start, goff, c->d_hashes.as<uint32_t>());

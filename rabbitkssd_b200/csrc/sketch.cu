@@ -48,6 +48,7 @@ struct ScanArgs {
     uint64_t pos_base;
     unsigned long long *cursor;
     uint32_t *gcount;          // emitted keys per genome (sizes the per-genome segments of the shared-memory sort)
+    uint32_t *emit_rank;       // rank of emit[i] among the keys of its genome (= position inside the genome's segment)
     uint32_t n_genomes;
     uint64_t emit_cap;
     uint32_t n_tiles;
@@ -324,6 +325,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             unsigned long long at = 0;
             if (lane == 0) at = atomicAdd(a.cursor, (unsigned long long)__popc(m));
             at = __shfl_sync(FULL, at, 0) + __popc(m & lt);
+            uint32_t genome = 0xFFFFFFFFu;  // lanes without a key to store
             if (ok && at < a.emit_cap) {
                 const uint64_t gpos = a.pos_base + p;
                 uint32_t lo = 0, hi = a.n_seg;  // owning segment: largest s with seg_off[s] <= pos
@@ -331,9 +333,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
                     const uint32_t mid = (lo + hi) >> 1;
                     if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
                 }
-                const uint32_t genome = __ldg(a.seg_genome + lo);
+                genome = __ldg(a.seg_genome + lo);
                 a.emit[at] = ((unsigned long long)genome << 32) | hash;
-                if (genome < a.n_genomes) atomicAdd(a.gcount + genome, 1u);  // emits are rare (one per ~16^l bases): no aggregation needed
+                if (genome >= a.n_genomes) genome = 0xFFFFFFFFu;  // not a genome of this session: never dealt
+            }
+            // rank of the key inside its genome = running per-genome count; survivors of one warp almost always belong
+            // to one genome, so one atomic per genome per warp (the counters are hot: all SMs stream the same genome)
+            const uint32_t peers = __match_any_sync(FULL, genome);
+            if (genome != 0xFFFFFFFFu) {
+                const int leader = __ffs(peers) - 1;
+                uint32_t base = 0;
+                if (lane == leader) base = atomicAdd(a.gcount + genome, (uint32_t)__popc(peers));
+                base = __shfl_sync(peers, base, leader);
+                a.emit_rank[at] = base + __popc(peers & lt);
             }
         }
     };
@@ -565,6 +577,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.n_seg = n_seg;
     a.cursor = c->d_cursor.as<unsigned long long>();
     a.gcount = c->d_gcount.as<uint32_t>();
+    a.emit_rank = c->d_emit_rank.as<uint32_t>();
     a.n_genomes = c->n_genomes;
     a.emit_cap = c->emit_cap;
     a.sp = sp;
