@@ -46,42 +46,45 @@ __device__ __forceinline__ void bitonic_sort_smem(K *s, uint32_t n) {
 }
 
 // Counting-bucket sort of n keys from global memory into shared memory: hashes are uniform, so NB >= n/4 buckets on
-// the leading key bits hold a handful of keys each -- one shared-memory atomic to count, one to place, and a
-// per-thread insertion sort of each tiny bucket, instead of the ~log^2(n)/2 compare-exchange rounds of the bitonic
-// network (which remains the fallback when some bucket is crowded, e.g. one hash shared by a thousand genomes).
-// bucket(key) must be non-decreasing in key and < NB.  cnt: NB counters.  On return dst[0, n) is sorted.
+// the leading key bits hold a handful of keys each -- one shared-memory atomic to count, one to place, then every
+// bucket with >= 2 keys is rank-sorted by a warp (lane = member: rank = number of smaller members), instead of the
+// ~log^2(n)/2 compare-exchange rounds of the bitonic network (which remains the fallback when some bucket holds
+// more than 32 keys, e.g. one hash shared by a thousand genomes).
+// bucket(key) must be non-decreasing in key and < NB.  NB: power of two >= 32.  cnt: NB counters.
+// On return dst[0, n) is sorted.
 template <typename K, typename F>
 __device__ __forceinline__ void count_sort_smem(const K *src, K *dst, uint32_t *cnt, uint32_t n, uint32_t NB, F bucket) {
     __shared__ uint32_t cs_warp[32];
-    __shared__ uint32_t cs_carry, cs_max;
+    __shared__ uint32_t cs_max;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     for (uint32_t i = threadIdx.x; i < NB; i += blockDim.x) cnt[i] = 0;
-    if (threadIdx.x == 0) { cs_carry = 0; cs_max = 0; }
+    if (threadIdx.x == 0) cs_max = 0;
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(cnt + bucket(src[i]), 1u);
     __syncthreads();
-    uint32_t mx = 0;
-    for (uint32_t base = 0; base < NB; base += blockDim.x) {  // exclusive scan of the counters, in place
-        const uint32_t i = base + threadIdx.x;
-        const uint32_t v = i < NB ? cnt[i] : 0;
-        mx = max(mx, v);
-        uint32_t x = v;
+    {   // exclusive scan of the counters, in place: thread t owns `per` consecutive counters
+        const uint32_t per = NB > blockDim.x ? NB / blockDim.x : 1;  // both powers of two
+        const uint32_t first = threadIdx.x * per;
+        uint32_t sum = 0, mx = 0;
+        if (first < NB)
+            for (uint32_t q = 0; q < per; q++) { const uint32_t v = cnt[first + q]; sum += v; mx = max(mx, v); }
+        uint32_t x = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
             if (lane >= o) x += y;
         }
+        for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
         if (lane == 31) cs_warp[w] = x;
+        if (lane == 0 && mx) atomicMax(&cs_max, mx);
         __syncthreads();
-        uint32_t wp = 0, tot = 0;
-        for (int q = 0; q < n_warps; q++) { const uint32_t t = cs_warp[q]; if (q < w) wp += t; tot += t; }
-        if (i < NB) cnt[i] = cs_carry + wp + x - v;
+        uint32_t wp = 0;
+        for (int q = 0; q < w; q++) wp += cs_warp[q];
+        uint32_t run = wp + x - sum;
+        if (first < NB)
+            for (uint32_t q = 0; q < per; q++) { const uint32_t v = cnt[first + q]; cnt[first + q] = run; run += v; }
         __syncthreads();
-        if (threadIdx.x == 0) cs_carry += tot;
     }
-    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
-    if (lane == 0 && mx) atomicMax(&cs_max, mx);
-    __syncthreads();
     if (cs_max > 32) {  // crowded bucket: sort the whole segment with the network instead
         for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
         __syncthreads();
@@ -93,33 +96,53 @@ __device__ __forceinline__ void count_sort_smem(const K *src, K *dst, uint32_t *
         dst[atomicAdd(cnt + bucket(k), 1u)] = k;
     }
     __syncthreads();
-    for (uint32_t b = threadIdx.x; b < NB; b += blockDim.x) {  // cnt[b] is now the END of bucket b
-        const uint32_t beg = b ? cnt[b - 1] : 0, end = cnt[b];
-        for (uint32_t i = beg + 1; i < end; i++) {
-            const K k = dst[i];
-            uint32_t j = i;
-            while (j > beg && dst[j - 1] > k) { dst[j] = dst[j - 1]; j--; }
-            dst[j] = k;
+    // cnt[b] is now the END of bucket b.  Warps walk the buckets 32 at a time and rank-sort those with >= 2 keys.
+    for (uint32_t b0 = (uint32_t)w * 32; b0 < NB; b0 += (uint32_t)n_warps * 32) {
+        const uint32_t b = b0 + lane;
+        const uint32_t end = cnt[b], beg = b ? cnt[b - 1] : 0;
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, end - beg >= 2);
+        while (todo) {
+            const int src_lane = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t bb = __shfl_sync(0xFFFFFFFFu, beg, src_lane), m = __shfl_sync(0xFFFFFFFFu, end, src_lane) - bb;
+            K k = 0;
+            uint32_t rank = 0;
+            if ((uint32_t)lane < m) {
+                k = dst[bb + lane];
+                for (uint32_t i = 0; i < m; i++) {
+                    const K o = dst[bb + i];
+                    rank += (o < k) || (o == k && i < (uint32_t)lane);
+                }
+            }
+            __syncwarp();
+            if ((uint32_t)lane < m) dst[bb + rank] = k;
+            __syncwarp();
         }
     }
     __syncthreads();
 }
 
-// counts[n] -> start[n+1] (exclusive, 64-bit), *max_out = largest count.  Single CTA.
+// counts[n] -> start[n+1] (exclusive, 64-bit), *max_out = largest count.  Single CTA; a thread owns 16 consecutive
+// counts per round, so 16 k segments need one round (two barriers).
 __global__ void __launch_bounds__(1024) segment_scan_kernel(const uint32_t *__restrict__ counts, uint32_t n, uint64_t *__restrict__ start,
                                                             uint32_t *__restrict__ max_out) {
+    constexpr int kItems = 16;
     __shared__ uint64_t warp_sums[32];
     __shared__ uint32_t warp_max[32];
-    __shared__ uint64_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t mx = 0;
-    for (uint32_t base = 0; base < n; base += 1024) {
-        const uint32_t i = base + threadIdx.x;
-        const uint64_t v = i < n ? counts[i] : 0;
-        mx = max(mx, (uint32_t)v);
-        uint64_t x = v;
+    uint64_t carry = 0;  // kept identically by every thread
+    for (uint32_t base = 0; base < n; base += 1024 * kItems) {
+        const uint32_t first = base + threadIdx.x * kItems;
+        uint32_t v[kItems];
+        uint64_t sum = 0;
+#pragma unroll
+        for (int q = 0; q < kItems; q++) {
+            v[q] = first + q < n ? counts[first + q] : 0;
+            sum += v[q];
+            mx = max(mx, v[q]);
+        }
+        uint64_t x = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint64_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
@@ -127,12 +150,15 @@ __global__ void __launch_bounds__(1024) segment_scan_kernel(const uint32_t *__re
         }
         if (lane == 31) warp_sums[w] = x;
         __syncthreads();
-        uint64_t wp = 0;
-        for (int q = 0; q < w; q++) wp += warp_sums[q];
-        const uint64_t excl = carry + wp + x - v;
-        if (i < n) start[i] = excl;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
+        uint64_t wp = 0, tot = 0;
+        for (int q = 0; q < 32; q++) { const uint64_t t = warp_sums[q]; if (q < w) wp += t; tot += t; }
+        uint64_t run = carry + wp + x - sum;
+#pragma unroll
+        for (int q = 0; q < kItems; q++) {
+            if (first + q < n) start[first + q] = run;
+            run += v[q];
+        }
+        carry += tot;
         __syncthreads();
     }
     for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
