@@ -18,107 +18,49 @@ namespace kssd {
 
 // ---- step 1: per query hash, the posting range it has to stream --------------------------------------------
 // grid = (rows, chunks): the row is known from blockIdx.x, so nothing is searched but the hash itself (a coarse
-// directory narrows it to a handful of distinct hashes) and, for alldist, the first posting id > row.  The kernel is
-// a chain of dependent L2 reads (hash -> directory -> distinct hashes -> list offsets -> postings), so a thread works
-// on kLookupIlp hashes in lock step and every stage is a fixed window of predicated, independent loads; the rare
-// bucket / list longer than the window takes a binary search.
-static constexpr int kLookupIlp = 4;
-static constexpr int kLookupThreads = 128;
-static constexpr uint32_t kLookupWin = 8;
-
-__global__ void __launch_bounds__(kLookupThreads) list_lookup_kernel(const uint32_t *__restrict__ q_hashes, const uint64_t *__restrict__ q_off,
-                                                                     uint32_t row_begin, const uint32_t *__restrict__ uniq_hash,
-                                                                     const uint64_t *__restrict__ uniq_off, const uint32_t *__restrict__ bucket,
-                                                                     int bucket_shift, uint32_t n_buckets, const uint32_t *__restrict__ dict,
-                                                                     int triangle, uint32_t *__restrict__ lb, uint32_t *__restrict__ le,
-                                                                     unsigned long long *__restrict__ posting_total) {
+// directory narrows it to a handful of distinct hashes) and, for alldist, the first posting id > row.
+__global__ void __launch_bounds__(128) list_lookup_kernel(const uint32_t *__restrict__ q_hashes, const uint64_t *__restrict__ q_off,
+                                                          uint32_t row_begin, const uint32_t *__restrict__ uniq_hash,
+                                                          const uint64_t *__restrict__ uniq_off, const uint32_t *__restrict__ bucket,
+                                                          int bucket_shift, uint32_t n_buckets, const uint32_t *__restrict__ dict,
+                                                          int triangle, uint32_t *__restrict__ lb, uint32_t *__restrict__ le,
+                                                          unsigned long long *__restrict__ posting_total) {
     const uint32_t row = row_begin + blockIdx.x;
     const uint64_t e_base = q_off[row_begin];
     const uint64_t e0 = q_off[row], e1 = q_off[row + 1];
     unsigned long long s = 0;
-    constexpr uint32_t kStep = kLookupThreads * kLookupIlp;
-    for (uint64_t eb = e0 + (uint64_t)blockIdx.y * kStep; eb < e1; eb += (uint64_t)gridDim.y * kStep) {
-        uint64_t e[kLookupIlp];
-        bool live[kLookupIlp];
-        uint32_t h[kLookupIlp], lo[kLookupIlp], hi[kLookupIlp], pos[kLookupIlp], b[kLookupIlp], en[kLookupIlp];
-        bool found[kLookupIlp];
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {
-            e[k] = eb + (uint64_t)k * kLookupThreads + threadIdx.x;
-            live[k] = e[k] < e1;
-            h[k] = live[k] ? q_hashes[e[k]] : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {
-            const uint32_t bk = h[k] >> bucket_shift;
-            live[k] = live[k] && bk < n_buckets;  // hashes above the largest indexed one have no bucket
-            lo[k] = live[k] ? bucket[bk] : 0u;
-            hi[k] = live[k] ? bucket[bk + 1] : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {  // window over the bucket: position = number of smaller distinct hashes
-            uint32_t less = 0;
-            bool eq = false;
-#pragma unroll
-            for (uint32_t i = 0; i < kLookupWin; i++) {
-                const uint32_t idx = lo[k] + i;
-                const uint32_t v = idx < hi[k] ? uniq_hash[idx] : 0xFFFFFFFFu;
-                less += idx < hi[k] && v < h[k];
-                eq = eq || (idx < hi[k] && v == h[k]);
+    for (uint64_t e = e0 + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
+        const uint32_t h = q_hashes[e];
+        const uint32_t bk = h >> bucket_shift;
+        uint32_t b = 0, en = 0;
+        if (bk < n_buckets) {  // hashes above the largest indexed one have no bucket
+            uint32_t lo = bucket[bk], hi = bucket[bk + 1];
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (uniq_hash[mid] < h) lo = mid + 1; else hi = mid;
             }
-            pos[k] = lo[k] + less;
-            found[k] = eq;
-        }
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {
-            if (hi[k] - lo[k] > kLookupWin) {  // rare: crowded bucket
-                uint32_t l = lo[k], r = hi[k];
-                while (l < r) {
-                    const uint32_t mid = (l + r) >> 1;
-                    if (uniq_hash[mid] < h[k]) l = mid + 1; else r = mid;
-                }
-                pos[k] = l;
-                found[k] = l < hi[k] && uniq_hash[l] == h[k];
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {
-            b[k] = found[k] ? (uint32_t)uniq_off[pos[k]] : 0u;
-            en[k] = found[k] ? (uint32_t)uniq_off[pos[k] + 1] : 0u;
-        }
-        if (triangle) {  // first posting id > row (ids ascending inside a list)
-            uint32_t skip[kLookupIlp];
-#pragma unroll
-            for (int k = 0; k < kLookupIlp; k++) {
-                skip[k] = 0;
-#pragma unroll
-                for (uint32_t i = 0; i < kLookupWin; i++) {
-                    const uint32_t p = b[k] + i;
-                    skip[k] += p < en[k] && dict[p < en[k] ? p : b[k]] <= row;
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < kLookupIlp; k++) {
-                if (en[k] - b[k] > kLookupWin) {  // long list
-                    uint32_t l = b[k], r = en[k];
-                    while (l < r) {
-                        const uint32_t mid = (l + r) >> 1;
-                        if (dict[mid] <= row) l = mid + 1; else r = mid;
+            if (lo < bucket[bk + 1] && uniq_hash[lo] == h) {
+                b = (uint32_t)uniq_off[lo];
+                en = (uint32_t)uniq_off[lo + 1];
+                if (triangle) {  // first posting id > row (ids ascending inside a list)
+                    if (en - b <= 8) {
+                        uint32_t skip = 0;
+                        for (uint32_t p = b; p < en; p++) skip += dict[p] <= row;  // independent loads
+                        b += skip;
+                    } else {
+                        uint32_t l2 = b, h2 = en;
+                        while (l2 < h2) {
+                            const uint32_t mid = (l2 + h2) >> 1;
+                            if (dict[mid] <= row) l2 = mid + 1; else h2 = mid;
+                        }
+                        b = l2;
                     }
-                    b[k] = l;
-                } else {
-                    b[k] += skip[k];
                 }
             }
         }
-#pragma unroll
-        for (int k = 0; k < kLookupIlp; k++) {
-            if (e[k] < e1) {
-                lb[e[k] - e_base] = b[k];
-                le[e[k] - e_base] = en[k];
-                s += en[k] - b[k];
-            }
-        }
+        lb[e - e_base] = b;
+        le[e - e_base] = en;
+        s += en - b;
     }
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
     if ((threadIdx.x & 31) == 0 && s) atomicAdd(posting_total, s);
@@ -339,8 +281,8 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     if (n_el) {
         const uint32_t n_rows_blk = row_end - row_begin;
         const uint64_t avg_len = n_el / n_rows_blk + 1;
-        const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + kLookupThreads * kLookupIlp - 1) / (kLookupThreads * kLookupIlp));
-        list_lookup_kernel<<<dim3(n_rows_blk, chunks), kLookupThreads, 0, st>>>(
+        const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);  // ~2 hashes per thread
+        list_lookup_kernel<<<dim3(n_rows_blk, chunks), 128, 0, st>>>(
             d_q_hashes, d_q_off, row_begin, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(),
             c->d_bucket.as<uint32_t>(), c->bucket_shift, c->n_buckets, c->d_dict.as<uint32_t>(), triangle, c->d_q_list_begin.as<uint32_t>(), c->d_q_list_end.as<uint32_t>(), d_post_total);
         KSSD_CUDA(cudaGetLastError());

@@ -46,8 +46,8 @@ __device__ __forceinline__ void bitonic_sort_smem(K *s, uint32_t n) {
 }
 
 // Counting-bucket sort of n keys from global memory into shared memory: hashes are uniform, so NB >= n/4 buckets on
-// the leading key bits hold a handful of keys each -- one shared-memory atomic to count, one to place, then every
-// bucket with >= 2 keys is rank-sorted by a warp (lane = member: rank = number of smaller members), instead of the
+// the leading key bits hold a handful of keys each -- one shared-memory atomic to count, one to place, then a
+// per-thread insertion sort of each tiny bucket, instead of the
 // ~log^2(n)/2 compare-exchange rounds of the bitonic network (which remains the fallback when some bucket holds
 // more than 32 keys, e.g. one hash shared by a thousand genomes).
 // bucket(key) must be non-decreasing in key and < NB.  NB: power of two >= 32.  cnt: NB counters.
@@ -96,27 +96,13 @@ __device__ __forceinline__ void count_sort_smem(const K *src, K *dst, uint32_t *
         dst[atomicAdd(cnt + bucket(k), 1u)] = k;
     }
     __syncthreads();
-    // cnt[b] is now the END of bucket b.  Warps walk the buckets 32 at a time and rank-sort those with >= 2 keys.
-    for (uint32_t b0 = (uint32_t)w * 32; b0 < NB; b0 += (uint32_t)n_warps * 32) {
-        const uint32_t b = b0 + lane;
-        const uint32_t end = cnt[b], beg = b ? cnt[b - 1] : 0;
-        uint32_t todo = __ballot_sync(0xFFFFFFFFu, end - beg >= 2);
-        while (todo) {
-            const int src_lane = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const uint32_t bb = __shfl_sync(0xFFFFFFFFu, beg, src_lane), m = __shfl_sync(0xFFFFFFFFu, end, src_lane) - bb;
-            K k = 0;
-            uint32_t rank = 0;
-            if ((uint32_t)lane < m) {
-                k = dst[bb + lane];
-                for (uint32_t i = 0; i < m; i++) {
-                    const K o = dst[bb + i];
-                    rank += (o < k) || (o == k && i < (uint32_t)lane);
-                }
-            }
-            __syncwarp();
-            if ((uint32_t)lane < m) dst[bb + rank] = k;
-            __syncwarp();
+    for (uint32_t b = threadIdx.x; b < NB; b += blockDim.x) {  // cnt[b] is now the END of bucket b: insertion sort inside
+        const uint32_t beg = b ? cnt[b - 1] : 0, end = cnt[b];
+        for (uint32_t i = beg + 1; i < end; i++) {
+            const K k = dst[i];
+            uint32_t j = i;
+            while (j > beg && dst[j - 1] > k) { dst[j] = dst[j - 1]; j--; }
+            dst[j] = k;
         }
     }
     __syncthreads();

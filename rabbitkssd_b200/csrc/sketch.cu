@@ -55,6 +55,7 @@ struct ScanArgs {
     uint32_t n_interior;       // tiles [1, n_interior) lie completely inside the buffer (halo included)
     uint32_t bitmap_words;
     uint32_t addr_mask;        // ((1<<wbits)-1) << 2
+    uint32_t mul29;            // 1u << 29
     int preshift;              // bit offset (mod 32) of the first index base of test 0 inside [P0,P1,A0,A1]
     int least_qual;
     int aligned32;             // seq is 32-byte aligned: tiles are read with 256-bit loads
@@ -280,27 +281,28 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     uint32_t *cand_pos = s_mem + a.bitmap_words + kL2Words + kScanWarps * kQueueCap * 4 + warp * kQueueCap;
     uint32_t *ver_pos = cand_pos + kScanWarps * kQueueCap;
     const uint32_t tile_stride = gridDim.x * kScanWarps;
-    // interleave warps of different CTAs over consecutive tiles so that all SMs stream the same HBM region
-    uint32_t tile = (uint32_t)warp * gridDim.x + blockIdx.x;
+    // round k: CTA c owns the 32 consecutive tiles [(k * grid + c) * 32, +32), one per warp -- all SMs stream one
+    // contiguous window of HBM, and a CTA's next-but-one window is ONE contiguous block that warp 0 pulls into L2
+    uint32_t tile = blockIdx.x * kScanWarps + (uint32_t)warp;
     if (tile >= a.n_tiles) return;
     const uint32_t addr_mask = a.addr_mask;
+    const uint32_t mul29 = a.mul29;  // 1 << 29, from the parameter block so that it is not folded back into a shift
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
     uint32_t lt;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
     const int lane_off = (lane - 1) * kLaneBases;
-    const uint8_t *lane_ptr = a.seq + lane_off;  // lane 0: before the tile (halo)
     int n_cand = 0, n_ver = 0;
     // 32-bit shared-window addresses of this warp's queues (kept in registers; the enqueue round is hot)
     uint32_t cand_pos_sa = (uint32_t)__cvta_generic_to_shared(cand_pos);
     uint32_t cand_s_sa = (uint32_t)__cvta_generic_to_shared(cand_s);
     uint32_t lane_off_u = (uint32_t)lane_off;
     // opaque to the optimiser: otherwise it re-derives these from threadIdx / kernel parameters in every round
-    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off_u), "+l"(lane_ptr));
+    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off_u));
 
     auto load_tile = [&](uint32_t tl, uint4 &v0, uint4 &v1) {
         if (tl >= 1 && tl < a.n_interior) {
-            const uint8_t *p = lane_ptr + (size_t)tl * kTileBytes;
+            const uint8_t *p = a.seq + (tl * kTileBytes + lane_off_u);  // 32-bit offset (>= 960 here): one IMAD + one 64-bit add
             if (a.aligned32) {
                 ldg256(p, v0, v1);
             } else {
@@ -381,11 +383,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         tile += tile_stride;
         const bool more = tile < a.n_tiles;
         if (more) load_tile(tile, cur0, cur1);
-        {   // pull the tile after that into L2 (one bulk prefetch per warp): the register prefetch above then pays
-            // L2 latency instead of HBM latency
-            const uint32_t far_tile = tile + tile_stride;
-            if (lane == 0 && far_tile < a.n_interior)
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.seq + (size_t)far_tile * kTileBytes), "r"(1024) : "memory");
+        if (threadIdx.x == 0) {   // pull the CTA's window after the next into L2 (one bulk prefetch per CTA and round): the
+            // register prefetch above then pays L2 latency instead of HBM latency
+            const uint32_t far_tile = tile + tile_stride;  // warp 0: first tile of that window
+            if (far_tile + kScanWarps <= a.n_interior)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.seq + (size_t)far_tile * kTileBytes), "r"(kScanWarps * kTileBytes) : "memory");
         }
         const uint32_t P0 = __shfl_up_sync(FULL, A0, 1), P1 = __shfl_up_sync(FULL, A1, 1);
         // S = [P0, P1, A0, A1, 0] shifted so that bit 0 is the first index base of test 0
@@ -408,7 +410,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             const int wd = off >> 5, sh = off & 31;
             const uint32_t lo = wd == 0 ? S0 : S1, hi = wd == 0 ? S1 : S2;
             const uint32_t x = sh == 0 ? lo : __funnelshift_r(lo, hi, sh);
-            const uint32_t word = *reinterpret_cast<const uint32_t *>(smem_base + ((x >> 3) & addr_mask));
+            // x >> 3 as a multiply-high: runs on the FMA pipe, the ALU pipe is the one that is full
+            uint32_t x3;
+            asm("mul.hi.u32 %0, %1, %2;" : "=r"(x3) : "r"(x), "r"(mul29));
+            const uint32_t word = *reinterpret_cast<const uint32_t *>(smem_base + (x3 & addr_mask));
             const uint32_t tt = __funnelshift_l(0u, word, x);  // word << (x & 31): tested bit -> MSB
             hit = __funnelshift_l(tt, hit, 1);                 // hit = hit << 1 | msb(tt)
         }
@@ -420,7 +425,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             const uint32_t lane_pos = this_tile * kTileBytes + lane_off_u;
             const uint4 sw = make_uint4(P0, P1, A0, A1);
             do {
-                if (hit) {
+                const bool mine = hit != 0;
+                if (mine) {
                     const int t = __ffs(hit) - 1;
                     hit &= hit - 1;
                     const uint32_t slot = (uint32_t)n_cand + __popc(any & lt);
@@ -428,8 +434,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
                     sts128(cand_s_sa + slot * 16, sw);
                 }
                 n_cand += __popc(any);
-                __syncwarp();
                 if (n_cand >= 32) {
+                    __syncwarp();
                     n_cand -= 32;
                     stage1(n_cand, 32);
                     __syncwarp();
@@ -440,6 +446,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
 
         if (!more) break;
     }
+    __syncwarp();
     if (n_cand) stage1(0, n_cand);
     __syncwarp();
     if (n_ver) stage2(0, n_ver);
@@ -583,6 +590,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.sp = sp;
     a.bitmap_words = (uint32_t)std::max<uint64_t>((1ull << (2 * sp.nb)) / 32, 4);
     a.addr_mask = ((1u << sp.wbits) - 1) << 2;
+    a.mul29 = 1u << 29;
     a.preshift = bit0 & 31;
     a.least_qual = c->least_qual;
     const int w0 = bit0 >> 5;
