@@ -130,21 +130,21 @@ static constexpr uint32_t kBucketCapSmall = 2048, kBucketCapLarge = 8192;  // pa
 static constexpr uint32_t kSubBuckets = 1024;                               // counting-sort buckets inside a bucket
 
 __global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, uint64_t total, int shift, uint32_t last_bucket,
-                                                          uint32_t *__restrict__ bcount) {
+                                                          uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < total) atomicAdd(bcount + min(hashes[i] >> shift, last_bucket), 1u);
+    if (i < total) rank[i] = atomicAdd(bcount + min(hashes[i] >> shift, last_bucket), 1u);  // arrival order inside the bucket
 }
 
-// grid = (genomes, chunks): the genome id is blockIdx.x
+// grid = (genomes, chunks): the genome id is blockIdx.x; the slot inside the bucket was drawn by the histogram pass
 __global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
-                                                          uint32_t last_bucket, const uint64_t *__restrict__ bstart, uint32_t *__restrict__ bcur,
+                                                          uint32_t last_bucket, const uint64_t *__restrict__ bstart, const uint32_t *__restrict__ rank,
                                                           uint64_t *__restrict__ pairs) {
     const uint32_t g = blockIdx.x;
     const uint64_t e1 = genome_off[g + 1];
     for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
         const uint32_t h = hashes[e];
         const uint32_t b = min(h >> shift, last_bucket);
-        pairs[bstart[b] + atomicAdd(bcur + b, 1u)] = ((uint64_t)h << 32) | g;
+        pairs[bstart[b] + rank[e]] = ((uint64_t)h << 32) | g;
     }
 }
 
@@ -241,10 +241,10 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     uint32_t *tmp_hash = c->d_pairs_tmp.as<uint32_t>();
     uint32_t *tmp_rel = tmp_hash + total;
     const uint64_t avg_len = total / n_genomes + 1;
-    const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, std::min<uint64_t>(avg_len / 512, (4ull * c->sm_count * 16) / n_genomes)));
-    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, bcount);
+    const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);
+    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, bcount, tmp_hash /* rank, dead before the sort */);
     segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
-    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, bstart, bcur, c->d_pairs.as<uint64_t>());
+    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, bstart, tmp_hash, c->d_pairs.as<uint64_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
     static bool attr_done = false;

@@ -7,9 +7,9 @@
 //
 //   filter (every base)
 //   * a lane owns 32 bases: one 256-bit load (LDG.E.256), the next tile is loaded into the same registers as soon
-//     as the bytes are packed and the tile after that is pulled into L2 with one bulk prefetch per warp; lane 0
-//     of the warp re-reads the 32 bases before the tile as halo, so no state is carried between tiles
-//     (tile = 31 x 32 = 992 new bytes per warp);
+//     as the bytes are packed (register prefetch one round ahead, no L2 prefetch); lane 0 of the warp re-reads
+//     the 32 bases before the tile as halo, so no state is carried between tiles (tile = 31 x 32 = 992 new
+//     bytes per warp);
 //   * 4 ASCII bytes -> 8 bits with one AND and one IMAD ((x & 0x06060606) * M gathers bits 1-2 of each byte:
 //     A/a 0, C/c 1, T/t 2, G/g 3).  Validity (N, separators, quality) is NOT decided here;
 //   * membership of the 2s-mer is tested WITHOUT deciding the canonical strand and for G consecutive k-mer end
@@ -58,7 +58,6 @@ struct ScanArgs {
     uint32_t mul29;            // 1u << 29
     int preshift;              // bit offset (mod 32) of the first index base of test 0 inside [P0,P1,A0,A1]
     int least_qual;
-    int aligned32;             // seq is 32-byte aligned: tiles are read with 256-bit loads
     ScanParams sp;
 };
 
@@ -261,7 +260,8 @@ __device__ __forceinline__ uint32_t screen_group(const ScanArgs &a, const uint32
 }
 
 // G: k-mer end positions decided per bitmap test.  W0: word offset (0/1) of the first index base of test 0.
-template <int G, int W0>
+// A32: seq is 32-byte aligned, tiles are read with one 256-bit load per lane.
+template <int G, int W0, bool A32>
 __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid_constant__ ScanArgs a) {
     extern __shared__ uint4 s_mem4[];
     uint32_t *s_mem = reinterpret_cast<uint32_t *>(s_mem4);
@@ -282,38 +282,42 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     uint32_t *ver_pos = cand_pos + kScanWarps * kQueueCap;
     const uint32_t tile_stride = gridDim.x * kScanWarps;
     // round k: CTA c owns the 32 consecutive tiles [(k * grid + c) * 32, +32), one per warp -- all SMs stream one
-    // contiguous window of HBM, and a CTA's next-but-one window is ONE contiguous block that warp 0 pulls into L2
-    uint32_t tile = blockIdx.x * kScanWarps + (uint32_t)warp;
-    if (tile >= a.n_tiles) return;
+    // contiguous window of HBM.  No L2 prefetch: a bulk prefetch per CTA window re-read 40% of the bytes from DRAM
+    // (ncu, profiles/r01m_scan_prefetch_variants.txt) and one per warp tile cost more issue slots than it saved latency.
+    // The loop variable is tile - 1 (tm1): "tm1 < n_interior - 1" is then the whole fast-path test (tile >= 1, tile and
+    // its halo inside the buffer, and therefore also tile < n_tiles) -- tile 0 wraps to 0xFFFFFFFF and fails it.
+    uint32_t tm1 = blockIdx.x * kScanWarps + (uint32_t)warp - 1u;
+    if (tm1 + 1u >= a.n_tiles) return;
+    const uint32_t n_int_m1 = a.n_interior ? a.n_interior - 1u : 0u;
     const uint32_t addr_mask = a.addr_mask;
     const uint32_t mul29 = a.mul29;  // 1 << 29, from the parameter block so that it is not folded back into a shift
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
     uint32_t lt;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
-    const int lane_off = (lane - 1) * kLaneBases;
     int n_cand = 0, n_ver = 0;
     // 32-bit shared-window addresses of this warp's queues (kept in registers; the enqueue round is hot)
     uint32_t cand_pos_sa = (uint32_t)__cvta_generic_to_shared(cand_pos);
     uint32_t cand_s_sa = (uint32_t)__cvta_generic_to_shared(cand_s);
-    uint32_t lane_off_u = (uint32_t)lane_off;
+    // byte offset of the lane's 32 bases from the start of tile tm1 (lane 0 = halo: the 32 bytes before tile tm1 + 1)
+    uint32_t lane_off1 = (uint32_t)((lane - 1) * kLaneBases + kTileBytes);
+    uint32_t keep = lane ? 0xFFFFFFFFu : 0u;  // halo lane: its positions belong to lane 31 of the previous tile
     // opaque to the optimiser: otherwise it re-derives these from threadIdx / kernel parameters in every round
-    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off_u));
+    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off1), "+r"(keep));
 
-    auto load_tile = [&](uint32_t tl, uint4 &v0, uint4 &v1) {
-        if (tl >= 1 && tl < a.n_interior) {
-            const uint8_t *p = a.seq + (tl * kTileBytes + lane_off_u);  // 32-bit offset (>= 960 here): one IMAD + one 64-bit add
-            if (a.aligned32) {
-                ldg256(p, v0, v1);
-            } else {
-                v0 = __ldg(reinterpret_cast<const uint4 *>(p));
-                v1 = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
-            }
+    auto load_fast = [&](uint32_t t1, uint4 &v0, uint4 &v1) {  // tile t1 + 1, interior
+        const uint8_t *p = a.seq + (t1 * kTileBytes + lane_off1);  // 32-bit offset: one IMAD + one 64-bit add
+        if (A32) {
+            ldg256(p, v0, v1);
         } else {
-            const int off = (int)(tl * kTileBytes) + lane_off;
-            v0 = load_chunk(a.seq, off, a.n_bytes);
-            v1 = load_chunk(a.seq, off + 16, a.n_bytes);
+            v0 = __ldg(reinterpret_cast<const uint4 *>(p));
+            v1 = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
         }
+    };
+    auto load_edge = [&](uint32_t tl, uint4 &v0, uint4 &v1) {  // first / last tiles: bytes outside the buffer read as 0
+        const int off = (int)(tl * kTileBytes) + (lane - 1) * kLaneBases;
+        v0 = load_chunk(a.seq, off, a.n_bytes);
+        v1 = load_chunk(a.seq, off + 16, a.n_bytes);
     };
     auto stage2 = [&](int base, int n) {  // exact path for queued positions [base, base+n), append survivors to the emit buffer
         uint32_t p = 0, hash = 0;
@@ -373,21 +377,20 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     };
 
     uint4 cur0, cur1;
-    load_tile(tile, cur0, cur1);
+    if (tm1 < n_int_m1) load_fast(tm1, cur0, cur1); else load_edge(tm1 + 1u, cur0, cur1);
 
     while (true) {
         // ---- 32 bases -> 2 x 32 bits; the raw bytes are dead after this, so the SAME registers receive the next
         //      tile right away (software pipelining without a second register set or copies) ----
         const uint32_t A0 = pack16_filter(cur0), A1 = pack16_filter(cur1);
-        const uint32_t this_tile = tile;
-        tile += tile_stride;
-        const bool more = tile < a.n_tiles;
-        if (more) load_tile(tile, cur0, cur1);
-        if (threadIdx.x == 0) {   // pull the CTA's window after the next into L2 (one bulk prefetch per CTA and round): the
-            // register prefetch above then pays L2 latency instead of HBM latency
-            const uint32_t far_tile = tile + tile_stride;  // warp 0: first tile of that window
-            if (far_tile + kScanWarps <= a.n_interior)
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.seq + (size_t)far_tile * kTileBytes), "r"(kScanWarps * kTileBytes) : "memory");
+        const uint32_t this_tm1 = tm1;
+        tm1 += tile_stride;
+        bool more = true;
+        if (tm1 < n_int_m1) {
+            load_fast(tm1, cur0, cur1);
+        } else {
+            more = tm1 + 1u < a.n_tiles;
+            if (more) load_edge(tm1 + 1u, cur0, cur1);
         }
         const uint32_t P0 = __shfl_up_sync(FULL, A0, 1), P1 = __shfl_up_sync(FULL, A1, 1);
         // S = [P0, P1, A0, A1, 0] shifted so that bit 0 is the first index base of test 0
@@ -417,12 +420,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             const uint32_t tt = __funnelshift_l(0u, word, x);  // word << (x & 31): tested bit -> MSB
             hit = __funnelshift_l(tt, hit, 1);                 // hit = hit << 1 | msb(tt)
         }
-        if (lane == 0) hit = 0;  // halo lane: its positions belong to lane 31 of the previous tile
+        hit &= keep;
 
         // ---- queue the groups that passed (ballot + popc, no atomics); screen 32 at a time ----
         uint32_t any = __ballot_sync(FULL, hit != 0);
         if (any) {
-            const uint32_t lane_pos = this_tile * kTileBytes + lane_off_u;
+            const uint32_t lane_pos = this_tm1 * kTileBytes + lane_off1;
             const uint4 sw = make_uint4(P0, P1, A0, A1);
             do {
                 const bool mine = hit != 0;
@@ -529,17 +532,17 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
     return KSSD_OK;
 }
 
-template <int G, int W0>
+template <int G, int W0, bool A32>
 static int launch_one(kssd_ctx *c, const ScanArgs &a, size_t smem) {
     static bool attr_done = false;  // one flag per template instantiation
     if (!attr_done) {
-        KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+        KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0, A32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
         attr_done = true;
     }
     uint64_t ctas = std::min<uint64_t>(((uint64_t)a.n_tiles + kScanWarps - 1) / kScanWarps, (uint64_t)c->sm_count);
     if (ctas == 0) return KSSD_OK;
     if (c->profiling) KSSD_TRY(c->t_scan.begin(c->stream));
-    kssd_scan_kernel<G, W0><<<(unsigned)ctas, kScanThreads, smem, c->stream>>>(a);
+    kssd_scan_kernel<G, W0, A32><<<(unsigned)ctas, kScanThreads, smem, c->stream>>>(a);
     KSSD_CUDA(cudaGetLastError());
     if (c->profiling) KSSD_TRY(c->t_scan.end(c->stream));
     c->launches++;
@@ -549,8 +552,9 @@ static int launch_one(kssd_ctx *c, const ScanArgs &a, size_t smem) {
 }
 
 template <int G>
-static int launch_w0(kssd_ctx *c, const ScanArgs &a, size_t smem, int w0) {
-    return w0 ? launch_one<G, 1>(c, a, smem) : launch_one<G, 0>(c, a, smem);
+static int launch_w0(kssd_ctx *c, const ScanArgs &a, size_t smem, int w0, bool a32) {
+    if (a32) return w0 ? launch_one<G, 1, true>(c, a, smem) : launch_one<G, 0, true>(c, a, smem);
+    return w0 ? launch_one<G, 1, false>(c, a, smem) : launch_one<G, 0, false>(c, a, smem);
 }
 
 int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
@@ -603,7 +607,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         const uint64_t from = b0 ? b0 - halo : 0;
         a.seq = d_seq + from;
         a.pos_base = pos_base + from;
-        a.aligned32 = (reinterpret_cast<uintptr_t>(a.seq) & 31) == 0;
+        const bool a32 = (reinterpret_cast<uintptr_t>(a.seq) & 31) == 0;
         a.qual = use_qual ? d_qual + from : nullptr;
         a.n_bytes = (uint32_t)(b1 - from);
         // k-mers ending inside the halo belong to the previous piece; the caller's first_emit applies to byte 0
@@ -613,10 +617,10 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
         a.n_interior = a.n_bytes / kTileBytes;
         int rc;
         switch (sp.group) {
-        case 1: rc = launch_w0<1>(c, a, smem, w0); break;
-        case 2: rc = launch_w0<2>(c, a, smem, w0); break;
-        case 3: rc = launch_w0<3>(c, a, smem, w0); break;
-        case 4: rc = launch_w0<4>(c, a, smem, w0); break;
+        case 1: rc = launch_w0<1>(c, a, smem, w0, a32); break;
+        case 2: rc = launch_w0<2>(c, a, smem, w0, a32); break;
+        case 3: rc = launch_w0<3>(c, a, smem, w0, a32); break;
+        case 4: rc = launch_w0<4>(c, a, smem, w0, a32); break;
         default: set_error("bad filter group %d", sp.group); return KSSD_E_ARG;
         }
         KSSD_TRY(rc);

@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Scan-kernel tuning run: times kssd_scan_kernel alone (CUDA events inside the library, device-resident input larger
+than L2) for several settings of its L2 prefetch (KSSD_B200_SCAN_PF="kind,dist", read by kssd_b200_init).
+usage: python scripts/scan_variants.py [--genomes 2000] [--steps 5] [--warmup 2] [--variants "1,1;0,0;2,2"]"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "oracle")]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--genomes", type=int, default=2000)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--variants", default="1,1;0,0;1,2;1,3;2,1;2,2;2,4")
+    args = ap.parse_args()
+    import numpy as np
+    import torch
+    import bench
+    import oracle
+    from rabbitkssd_b200 import api
+    length, family = 5_000_000, 10
+    stride = (length + 2 + 15) // 16 * 16  # as bench.py
+    n = args.genomes
+    buf = bench.gen_genomes_device(torch, n, 0, length, family, stride)
+    d_seg_off = torch.from_numpy((np.arange(n + 1, dtype=np.int64) * stride)).cuda()
+    d_seg_gen = torch.arange(n, dtype=torch.int32, device="cuda")
+    dim = oracle.shuffle_dim(bench.K, bench.S, bench.L_)
+    ref_tot = None
+    for v in args.variants.split(";"):
+        os.environ["KSSD_B200_SCAN_PF"] = v
+        ctx = api.Context(0)
+        ctx.set_params(bench.K, bench.S, bench.L_, dim)
+        ctx.set_profiling(True)
+        for i in range(args.warmup + args.steps):
+            if i == args.warmup:
+                ctx.sync()
+                ctx.scan_kernel_time()
+            ctx.sketch_begin(n)
+            ctx.scan_device(buf.data_ptr(), n * stride, d_seg_off.data_ptr(), d_seg_gen.data_ptr(), n)
+            _, _, tot = ctx.sketch_finish_device()
+        ms, launches, nbytes = ctx.scan_kernel_time()
+        if ref_tot is None:
+            ref_tot = tot
+        print(json.dumps({"pf": v, "ms_per_launch": ms / max(launches, 1), "launches": launches, "GBps": nbytes / ms / 1e6 if ms else None,
+                          "sketch_total": int(tot), "same_as_first": bool(tot == ref_tot)}), flush=True)
+        ctx.close()
+
+
+if __name__ == "__main__":
+    main()
