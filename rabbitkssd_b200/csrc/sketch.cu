@@ -61,6 +61,9 @@ struct ScanArgs {
     ScanParams sp;
 };
 
+#ifndef KSSD_ACC_FMA
+#define KSSD_ACC_FMA 0  // tests per lane whose hit bit is accumulated on the FMA pipe (tuning)
+#endif
 static constexpr int kScanThreads = 1024;
 static constexpr int kScanWarps = kScanThreads / 32;
 static constexpr int kLaneBases = 32;                          // bases owned by a lane
@@ -291,6 +294,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     const uint32_t n_int_m1 = a.n_interior ? a.n_interior - 1u : 0u;
     const uint32_t addr_mask = a.addr_mask;
     const uint32_t mul29 = a.mul29;  // 1 << 29, from the parameter block so that it is not folded back into a shift
+    const uint32_t two = a.mul29 >> 28;
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
     uint32_t lt;
@@ -302,8 +306,15 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     // byte offset of the lane's 32 bases from the start of tile tm1 (lane 0 = halo: the 32 bytes before tile tm1 + 1)
     uint32_t lane_off1 = (uint32_t)((lane - 1) * kLaneBases + kTileBytes);
     uint32_t keep = lane ? 0xFFFFFFFFu : 0u;  // halo lane: its positions belong to lane 31 of the previous tile
-    // opaque to the optimiser: otherwise it re-derives these from threadIdx / kernel parameters in every round
-    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa), "+r"(lane_off1), "+r"(keep));
+    // opaque to the optimiser AND to ptxas (which rematerialises anything it can re-derive from threadIdx in every
+    // round: S2R + 5 integer ops): bounce the per-lane constants through the warp's still-empty queue
+    asm volatile("" : "+r"(cand_pos_sa), "+r"(cand_s_sa));
+    sts32(cand_pos_sa + lane * 4, lane_off1);
+    sts32(cand_pos_sa + (32 + lane) * 4, keep);
+    __syncwarp();
+    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(lane_off1) : "r"(cand_pos_sa + lane * 4) : "memory");
+    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(keep) : "r"(cand_pos_sa + (32 + lane) * 4) : "memory");
+    __syncwarp();
 
     auto load_fast = [&](uint32_t t1, uint4 &v0, uint4 &v1) {  // tile t1 + 1, interior
         const uint8_t *p = a.seq + (t1 * kTileBytes + lane_off1);  // 32-bit offset: one IMAD + one 64-bit add
@@ -418,7 +429,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             asm("mul.hi.u32 %0, %1, %2;" : "=r"(x3) : "r"(x), "r"(mul29));
             const uint32_t word = *reinterpret_cast<const uint32_t *>(smem_base + (x3 & addr_mask));
             const uint32_t tt = __funnelshift_l(0u, word, x);  // word << (x & 31): tested bit -> MSB
-            hit = __funnelshift_l(tt, hit, 1);                 // hit = hit << 1 | msb(tt)
+            if (t < KSSD_ACC_FMA) {  // hit = hit * 2 + msb(tt) as two multiply-adds (FMA pipe) instead of one funnel shift (ALU pipe)
+                uint32_t h2;
+                asm("mul.lo.u32 %0, %1, %2;" : "=r"(h2) : "r"(hit), "r"(two));
+                asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(hit) : "r"(tt), "r"(two), "r"(h2));
+            } else {
+                hit = __funnelshift_l(tt, hit, 1);             // hit = hit << 1 | msb(tt)
+            }
         }
         hit &= keep;
 
