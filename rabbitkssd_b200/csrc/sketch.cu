@@ -61,9 +61,6 @@ struct ScanArgs {
     ScanParams sp;
 };
 
-#ifndef KSSD_ACC_FMA
-#define KSSD_ACC_FMA 0  // tests per lane whose hit bit is accumulated on the FMA pipe (tuning)
-#endif
 static constexpr int kScanThreads = 1024;
 static constexpr int kScanWarps = kScanThreads / 32;
 static constexpr int kLaneBases = 32;                          // bases owned by a lane
@@ -294,7 +291,6 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
     const uint32_t n_int_m1 = a.n_interior ? a.n_interior - 1u : 0u;
     const uint32_t addr_mask = a.addr_mask;
     const uint32_t mul29 = a.mul29;  // 1 << 29, from the parameter block so that it is not folded back into a shift
-    const uint32_t two = a.mul29 >> 28;
     const int r = a.preshift;
     const char *smem_base = reinterpret_cast<const char *>(s_bitmap);
     uint32_t lt;
@@ -429,13 +425,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             asm("mul.hi.u32 %0, %1, %2;" : "=r"(x3) : "r"(x), "r"(mul29));
             const uint32_t word = *reinterpret_cast<const uint32_t *>(smem_base + (x3 & addr_mask));
             const uint32_t tt = __funnelshift_l(0u, word, x);  // word << (x & 31): tested bit -> MSB
-            if (t < KSSD_ACC_FMA) {  // hit = hit * 2 + msb(tt) as two multiply-adds (FMA pipe) instead of one funnel shift (ALU pipe)
-                uint32_t h2;
-                asm("mul.lo.u32 %0, %1, %2;" : "=r"(h2) : "r"(hit), "r"(two));
-                asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(hit) : "r"(tt), "r"(two), "r"(h2));
-            } else {
-                hit = __funnelshift_l(tt, hit, 1);             // hit = hit << 1 | msb(tt)
-            }
+            hit = __funnelshift_l(tt, hit, 1);                 // hit = hit << 1 | msb(tt)
         }
         hit &= keep;
 

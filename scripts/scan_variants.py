@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Scan-kernel tuning run: times kssd_scan_kernel alone (CUDA events inside the library, device-resident input larger
-than L2) for several settings of its L2 prefetch (KSSD_B200_SCAN_PF="kind,dist", read by kssd_b200_init).
-usage: python scripts/scan_variants.py [--genomes 2000] [--steps 5] [--warmup 2] [--variants "1,1;0,0;2,2"]"""
+than L2) with the libkssd_b200.so that is in place; --tag labels the output line (scripts/run_variants.sh swaps in
+differently compiled libraries).
+usage: python scripts/scan_variants.py [--genomes 2000] [--steps 5] [--warmup 2] [--tag name]"""
 import argparse
 import json
 import os
@@ -16,7 +17,7 @@ def main():
     ap.add_argument("--genomes", type=int, default=2000)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
-    ap.add_argument("--variants", default="1,1;0,0;1,2;1,3;2,1;2,2;2,4")
+    ap.add_argument("--tag", default="default")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -31,8 +32,7 @@ def main():
     d_seg_gen = torch.arange(n, dtype=torch.int32, device="cuda")
     dim = oracle.shuffle_dim(bench.K, bench.S, bench.L_)
     ref_tot = None
-    for v in args.variants.split(";"):
-        os.environ["KSSD_B200_SCAN_PF"] = v
+    for v in [args.tag]:
         ctx = api.Context(0)
         ctx.set_params(bench.K, bench.S, bench.L_, dim)
         ctx.set_profiling(True)
@@ -46,7 +46,7 @@ def main():
         ms, launches, nbytes = ctx.scan_kernel_time()
         if ref_tot is None:
             ref_tot = tot
-        print(json.dumps({"pf": v, "ms_per_launch": ms / max(launches, 1), "launches": launches, "GBps": nbytes / ms / 1e6 if ms else None,
+        print(json.dumps({"lib": v, "ms_per_launch": ms / max(launches, 1), "launches": launches, "GBps": nbytes / ms / 1e6 if ms else None,
                           "sketch_total": int(tot), "same_as_first": bool(tot == ref_tot)}), flush=True)
         ctx.close()
 
