@@ -238,7 +238,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from rabbitkssd_b200 import api
-    from rabbitkssd_b200.multigpu import gather_sketches, triangle_bounds
+    from rabbitkssd_b200.multigpu import gather_sketches, gather_sketches_device, triangle_bounds
     import oracle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -270,7 +270,11 @@ def run_b200(args):
     d_seg_off = torch.from_numpy(seg_off_np.astype(np.int64)).cuda()
     d_seg_gen = torch.from_numpy(seg_gen_np.astype(np.int32)).cuda()
     n_bytes = n_local * stride
-    bounds = triangle_bounds(n_total, world)
+    sk_size = length / 16.0 ** L_                      # expected hashes per genome
+    gather_cap = int(1.25 * n_local * sk_size) + 1024  # block size of the sketch all-gather, the same on every rank
+    # rows cost their cells plus the posting-range lookups of their hashes (measured at N=1: list_lookup_kernel
+    # 0.031 us per hash, dist_tile_kernel 5.9e-6 us per cell -> ~5 cell-equivalents per hash)
+    bounds = triangle_bounds(n_total, world, row_cost=5.0 * sk_size)
     r0, r1 = bounds[rank], bounds[rank + 1]
     state = {}
 
@@ -293,9 +297,13 @@ def run_b200(args):
         if world > 1:
             h_loc = dev_tensor(torch, d_h, tot, torch.int32)
             o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
-            hashes, off = gather_sketches(dist, h_loc, o_loc[1:] - o_loc[:-1], world)
-            ph, po = hashes.data_ptr(), off.data_ptr()
-            state["keep"] = (hashes, off)
+            got = gather_sketches_device(dist, ctx, h_loc, o_loc[1:] - o_loc[:-1], world, gather_cap)
+            if got is not None:
+                ph, po, _ = got
+            else:  # some rank's shard exceeded the agreed block size: two-step gather with exact sizes
+                hashes, off = gather_sketches(dist, h_loc, o_loc[1:] - o_loc[:-1], world)
+                ph, po = hashes.data_ptr(), off.data_ptr()
+                state["keep"] = (hashes, off)
         else:
             ph, po = d_h, d_o
         t0 = mark("gather", t0)

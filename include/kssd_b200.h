@@ -98,6 +98,16 @@ int kssd_b200_sketch_finish(kssd_ctx *ctx, const uint32_t **hashes, const uint64
 /* Same, results stay in device memory (library owned). */
 int kssd_b200_sketch_finish_device(kssd_ctx *ctx, const uint32_t **d_hashes, const uint64_t **d_genome_off,
                                    uint64_t *total);
+/* Multi-GPU gather epilogue (the sketch shards of all ranks are all-gathered before the index is
+ * built; the reference has one address space, its counterpart is the `sketches` vector filled under omp critical,
+ * src/sketch.cpp:455-560).  d_parts (device) holds `world` blocks of stride_words u32 each, block r =
+ * [n_local per-genome sketch sizes][the hashes of rank r's genomes, genome-major][padding] -- what one all-gather
+ * of equally sized send buffers delivers.  Writes the concatenated CSR (world * n_local genomes, rank order) into
+ * library-owned device memory, valid until the next call.  *overflow != 0: some rank's shard did not fit its block
+ * (identical on every rank, so all ranks can fall back together); the outputs are then invalid. */
+int kssd_b200_sketch_concat_device(kssd_ctx *ctx, const uint32_t *d_parts, uint64_t stride_words, uint32_t n_local,
+                                   uint32_t world, const uint32_t **d_hashes, const uint64_t **d_genome_off,
+                                   uint64_t *total, int *overflow);
 
 /* ---- inverted index -----------------------------------------------------------------------------------
  * replaces transSketches, 32-bit path (src/sketch.cpp:970-1017): hash -> ascending genome ids.  The index is

@@ -127,6 +127,13 @@ class Context:
         check(self.lib.kssd_b200_sketch_finish_device(self.h, C.byref(hp), C.byref(op), C.byref(tot)))
         return hp.value or 0, op.value or 0, tot.value
 
+    def sketch_concat_device(self, d_parts, stride_words, n_local, world):
+        """Gather epilogue: `world` blocks [n_local sizes | hashes | padding] -> (d_hashes, d_genome_off, total, overflow)."""
+        ph, po, tot, ov = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_int()
+        check(self.lib.kssd_b200_sketch_concat_device(self.h, d_parts, stride_words, n_local, world, C.byref(ph), C.byref(po),
+                                                      C.byref(tot), C.byref(ov)))
+        return ph.value or 0, po.value or 0, tot.value, bool(ov.value)
+
     def sketch(self, seq, genome_off, qual=None, least_qual=0, least_num_kmer=1, batch_bytes=None):
         """Sketch a packed batch (rabbitkssd_b200.synth.pack_batch layout) through pinned host batches.
         genome_off[n+1]: byte offsets; genome g owns [genome_off[g], genome_off[g+1]).  Large inputs are cut into

@@ -135,7 +135,7 @@ void kssd_b200_destroy(kssd_ctx *c) {
                      &c->d_stage_seggen[1], &c->d_sort_tmp, &c->d_sort_counts, &c->d_keys_unique, &c->d_hashes, &c->d_genome_off,
                      &c->d_uniq_hash, &c->d_uniq_off, &c->d_dict, &c->d_ref_sizes, &c->d_pairs, &c->d_pairs_tmp, &c->d_bucket, &c->d_q_hashes,
                      &c->d_q_off, &c->d_q_list_begin, &c->d_q_list_end, &c->d_hits, &c->d_hit_cursor, &c->d_rowwork, &c->d_gcount, &c->d_seg_start, &c->d_ucount,
-                     &c->d_emit_rank};
+                     &c->d_emit_rank, &c->d_cat_hashes, &c->d_cat_off, &c->d_cat_counts};
     for (DevBuf *b : dev) b->release();
     HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits};
     for (HostBuf *b : host) b->release();

@@ -110,6 +110,7 @@ struct kssd_ctx {
     int batch_next = 0;
     kssd::DevBuf d_sort_tmp, d_sort_counts, d_keys_unique;
     kssd::DevBuf d_hashes, d_genome_off;
+    kssd::DevBuf d_cat_hashes, d_cat_off, d_cat_counts;  // sketch shards of all ranks, concatenated (multi-GPU gather epilogue)
     kssd::HostBuf h_hashes, h_genome_off, h_scalar;
     uint64_t sketch_total = 0;
 
@@ -145,6 +146,8 @@ int unique_keys(kssd_ctx *c, const uint64_t *d_sorted, uint64_t n, int min_count
                 uint64_t *n_out);
 int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uint32_t max_count, int min_count,
                        uint64_t *n_keep);   // segsort.cu: shared-memory per-genome sort + unique (fast path)
+int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total,
+                  int *overflow);  // segsort.cu: multi-GPU gather epilogue
 int genome_segments(kssd_ctx *c);           // segsort.cu: gcount -> seg_start + max count (no sync)
 int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_genomes, uint32_t *d_hashes,
                   uint64_t *d_genome_off);

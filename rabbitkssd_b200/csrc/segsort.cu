@@ -289,4 +289,52 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
     return KSSD_OK;
 }
 
+// ---- multi-GPU gather epilogue: concatenate the all-gathered sketch shards ---------------------------------------
+// parts = world blocks of stride u32: [n_local sizes][hashes, genome-major][padding].  No host round trip between
+// the all-gather and the index build: sizes -> counts (one array), segment_scan_kernel -> offsets, one CTA per
+// genome copies its hashes.
+__global__ void __launch_bounds__(256) concat_counts_kernel(const uint32_t *__restrict__ parts, uint64_t stride, uint32_t n_local, uint32_t n_total,
+                                                            uint32_t *__restrict__ counts) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n_total) counts[g] = parts[(uint64_t)(g / n_local) * stride + g % n_local];
+}
+
+__global__ void __launch_bounds__(128) concat_copy_kernel(const uint32_t *__restrict__ parts, uint64_t stride, uint32_t n_local,
+                                                          const uint64_t *__restrict__ off, uint32_t *__restrict__ out,
+                                                          unsigned long long *__restrict__ result /* [0] total, [1] overflow */) {
+    const uint32_t g = blockIdx.x;
+    const uint32_t r = g / n_local;
+    const uint64_t r0 = off[(uint64_t)r * n_local], r1 = off[(uint64_t)(r + 1) * n_local];
+    if (r1 - r0 > stride - n_local) {  // the shard of rank r did not fit its block: every genome of it reports, nothing is copied
+        if (threadIdx.x == 0 && g % n_local == 0) atomicExch(result + 1, 1ull);
+        return;
+    }
+    const uint64_t g0 = off[g], g1 = off[g + 1];
+    const uint32_t *src = parts + (uint64_t)r * stride + n_local + (g0 - r0);
+    for (uint64_t i = threadIdx.x; i < g1 - g0; i += blockDim.x) out[g0 + i] = src[i];
+    if (g == gridDim.x - 1 && threadIdx.x == 0) result[0] = g1;
+}
+
+int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow) {
+    cudaStream_t st = c->stream;
+    const uint32_t n_total = n_local * world;
+    const uint64_t result_word = ((uint64_t)n_total + 1) & ~1ull;  // [counts n_total][pad][result: total, overflow (u64 each)]
+    KSSD_TRY(c->d_cat_counts.reserve(result_word * 4 + 16, st));
+    KSSD_TRY(c->d_cat_off.reserve(((uint64_t)n_total + 1) * 8, st));
+    KSSD_TRY(c->d_cat_hashes.reserve(std::max<uint64_t>((stride - n_local) * world, 1) * 4, st));  // upper bound: every block full
+    unsigned long long *result = reinterpret_cast<unsigned long long *>(c->d_cat_counts.as<uint32_t>() + result_word);
+    KSSD_CUDA(cudaMemsetAsync(result, 0, 16, st));
+    concat_counts_kernel<<<(n_total + 255) / 256, 256, 0, st>>>(d_parts, stride, n_local, n_total, c->d_cat_counts.as<uint32_t>());
+    segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_cat_counts.as<uint32_t>(), n_total, c->d_cat_off.as<uint64_t>(), nullptr);
+    concat_copy_kernel<<<n_total, 128, 0, st>>>(d_parts, stride, n_local, c->d_cat_off.as<uint64_t>(), c->d_cat_hashes.as<uint32_t>(), result);
+    KSSD_CUDA(cudaGetLastError());
+    c->launches += 3;
+    KSSD_TRY(c->h_scalar.reserve(64));
+    KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, result, 16, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaStreamSynchronize(st));
+    *total = c->h_scalar.as<uint64_t>()[0];
+    *overflow = c->h_scalar.as<uint64_t>()[1] != 0;
+    return KSSD_OK;
+}
+
 }  // namespace kssd

@@ -7,15 +7,27 @@ gloo on CPUs (tests/test_multirank_gloo.py)."""
 import torch
 
 
-def triangle_bounds(n, parts):
-    """Row boundaries b[0..parts] that give every part (nearly) the same number of (row, col > row) cells of the
-    n x n triangle: row i costs n-1-i cells (src/dist.cpp:207 scans j in (i, n))."""
-    total = n * (n - 1) / 2.0
+def triangle_bounds(n, parts, row_cost=0.0):
+    """Row boundaries b[0..parts] that give every part (nearly) the same cost of the n x n triangle: row i costs
+    n-1-i cells (src/dist.cpp:207 scans j in (i, n)) plus row_cost cell-equivalents of per-row work (the posting-range
+    lookups of the row's hashes: list_lookup_kernel).  row_cost = 0 balances cells alone."""
+    if row_cost <= 0:
+        total = n * (n - 1) / 2.0
+        b = [0]
+        for p in range(1, parts):
+            target = total * p / parts
+            # cells in rows [0, r) = r*n - r(r+1)/2  -> solve for r
+            r = int(round(((2 * n - 1) - ((2 * n - 1) ** 2 - 8 * target) ** 0.5) / 2))
+            b.append(min(max(r, b[-1]), n))
+        b.append(n)
+        return b
+    # cost of rows [0, r) = r*(n + row_cost) - r(r+1)/2: same quadratic with n + row_cost in place of n
+    m = n + float(row_cost)
+    total = n * m - n * (n + 1) / 2.0
     b = [0]
     for p in range(1, parts):
         target = total * p / parts
-        # cells in rows [0, r) = r*n - r(r+1)/2  -> solve for r
-        r = int(round(((2 * n - 1) - ((2 * n - 1) ** 2 - 8 * target) ** 0.5) / 2))
+        r = int(round(((2 * m - 1) - ((2 * m - 1) ** 2 - 8 * target) ** 0.5) / 2))
         b.append(min(max(r, b[-1]), n))
     b.append(n)
     return b
@@ -28,6 +40,26 @@ def rect_bounds(n_query, parts):
     for p in range(parts):
         b.append(b[-1] + base + (1 if p < extra else 0))
     return b
+
+
+def gather_sketches_device(dist, ctx, hashes_local, sizes_local, world, cap):
+    """CUDA fast path of gather_sketches: ONE all-gather of equally sized blocks [n_local sizes | hashes | padding to
+    cap] and the library's concat kernels (kssd_b200_sketch_concat_device) -- no host round trip for the shard sizes,
+    no padded copy + cat.  cap: hashes per rank every rank agrees on beforehand (e.g. 1.25 x the expected sketch
+    size of its genomes).  Returns (d_hashes ptr, d_genome_off ptr, total): library-owned device memory, or None
+    when some rank's shard exceeded cap (the same answer on every rank: callers fall back to gather_sketches)."""
+    n_local = sizes_local.numel()
+    tot = hashes_local.numel()
+    dev = hashes_local.device
+    send = torch.empty(n_local + cap, dtype=torch.int32, device=dev)
+    send[:n_local] = sizes_local.to(torch.int32)
+    send[n_local:n_local + min(tot, cap)] = hashes_local[:cap]
+    recv = torch.empty(world * (n_local + cap), dtype=torch.int32, device=dev)
+    dist.all_gather_into_tensor(recv, send)
+    ph, po, total, overflow = ctx.sketch_concat_device(recv.data_ptr(), n_local + cap, n_local, world)
+    if overflow:
+        return None
+    return ph, po, total  # the concat call synchronised the stream: recv may be freed
 
 
 def gather_sketches(dist, hashes_local, sizes_local, world):

@@ -218,3 +218,41 @@ def test_sort_fallbacks_when_shared_memory_is_too_small():
         assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
     finally:
         c.close()
+
+
+def test_sketch_concat_device_matches_numpy():
+    """Multi-GPU gather epilogue (kssd_b200_sketch_concat_device): blocks [sizes | hashes | padding] of 3 simulated ranks
+    -> concatenated CSR; a shard larger than its block reports overflow."""
+    import torch
+    rng = np.random.default_rng(7)
+    world, n_local, cap = 3, 5, 4000
+    c = api.Context(0)
+    try:
+        sizes = rng.integers(0, 700, size=(world, n_local)).astype(np.uint32)
+        sizes[1, 2] = 0
+        parts = np.zeros((world, n_local + cap), dtype=np.uint32)
+        want = []
+        for r in range(world):
+            h = rng.integers(0, 2 ** 28, size=int(sizes[r].sum()), dtype=np.uint32)
+            parts[r, :n_local] = sizes[r]
+            parts[r, n_local:n_local + len(h)] = h
+            parts[r, n_local + len(h):] = 0xDEADBEEF
+            want.append(h)
+        want = np.concatenate(want)
+        d = torch.from_numpy(parts.view(np.int32)).cuda()
+        ph, po, total, overflow = c.sketch_concat_device(d.data_ptr(), n_local + cap, n_local, world)
+        assert not overflow and total == len(want)
+        class View:  # raw device pointer -> torch, no copy
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+        got_h = torch.as_tensor(View(ph, total, "<i4"), device="cuda")
+        got_o = torch.as_tensor(View(po, world * n_local + 1, "<i8"), device="cuda")
+        assert np.array_equal(got_h.cpu().numpy().view(np.uint32), want)
+        assert np.array_equal(got_o.cpu().numpy(), np.concatenate([[0], np.cumsum(sizes.reshape(-1).astype(np.int64))]))
+        # rank 1 claims more hashes than a block holds
+        parts[1, 0] = cap + 1
+        d = torch.from_numpy(parts.view(np.int32)).cuda()
+        _, _, _, overflow = c.sketch_concat_device(d.data_ptr(), n_local + cap, n_local, world)
+        assert overflow
+    finally:
+        c.close()

@@ -89,3 +89,17 @@ def test_partitions_cover_and_balance():
     b = multigpu.triangle_bounds(10000, 8)
     cells = [sum(10000 - 1 - i for i in range(b[p], b[p + 1])) for p in range(8)]
     assert max(cells) / (sum(cells) / 8) < 1.01
+
+
+def test_partitions_with_row_cost():
+    """row_cost > 0: every part gets the same cells + row_cost * rows; row_cost = 0 is the cells-only split."""
+    n, parts, rc = 10000, 8, 6000.0
+    b = multigpu.triangle_bounds(n, parts, row_cost=rc)
+    assert b[0] == 0 and b[-1] == n and all(x <= y for x, y in zip(b, b[1:]))
+    cost = [sum(n - 1 - i + rc for i in range(b[p], b[p + 1])) for p in range(parts)]
+    assert max(cost) / (sum(cost) / parts) < 1.01
+    assert multigpu.triangle_bounds(n, parts, row_cost=0.0) == multigpu.triangle_bounds(n, parts)
+    for nn in (1, 2, 7, 100):
+        for pp in (1, 2, 3, 8):
+            bb = multigpu.triangle_bounds(nn, pp, row_cost=3.0)
+            assert bb[0] == 0 and bb[-1] == nn and len(bb) == pp + 1 and all(x <= y for x, y in zip(bb, bb[1:]))
