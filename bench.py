@@ -238,7 +238,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from rabbitkssd_b200 import api
-    from rabbitkssd_b200.multigpu import gather_sketches, gather_sketches_device, triangle_bounds
+    from rabbitkssd_b200.multigpu import build_index_sharded, gather_sketches, gather_sketches_device, triangle_bounds
     import oracle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -299,15 +299,17 @@ def run_b200(args):
             o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
             got = gather_sketches_device(dist, ctx, h_loc, o_loc[1:] - o_loc[:-1], world, gather_cap)
             if got is not None:
-                ph, po, _ = got
+                ph, po, state["total_all"] = got
             else:  # some rank's shard exceeded the agreed block size: two-step gather with exact sizes
                 hashes, off = gather_sketches(dist, h_loc, o_loc[1:] - o_loc[:-1], world)
                 ph, po = hashes.data_ptr(), off.data_ptr()
                 state["keep"] = (hashes, off)
+                state["total_all"] = hashes.numel()
         else:
             ph, po = d_h, d_o
         t0 = mark("gather", t0)
-        ctx.index_build_device(ph, po, n_total)
+        if world == 1 or not build_index_sharded(dist, ctx, ph, po, n_total, state["total_all"], rank, world):
+            ctx.index_build_device(ph, po, n_total)
         t0 = mark("index", t0)
         d_hits, n_hits = ctx.dist_rows_device(ph, po, n_total, True, 2 * K, MAX_DIST, 0, rows=(r0, r1))
         t0 = mark("dist", t0)

@@ -124,6 +124,23 @@ int kssd_b200_index_export(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, con
  * counts = the dense count array of the .index file (hash_size entries), dict = the .dict payload. */
 int kssd_b200_index_load(kssd_ctx *ctx, uint64_t hash_size, const uint32_t *counts, const uint32_t *dict,
                          uint64_t total, const uint32_t *ref_sizes, uint32_t n_ref);
+/* Multi-GPU index build (north_star: "the reference index replicated by NCCL over NVLink"): rank
+ * `part` of `parts` builds the CSR of ONE hash range of transSketches' table (src/sketch.cpp:970-1017) from the
+ * sketches of ALL genomes (device pointers, as index_build) and packs it into d_block, block_words u32 of caller
+ * memory laid out for one all-gather of equally sized blocks: [distinct hashes U, postings P, max hash, 0,
+ * uniq_hash[U], list starts[U+1], postings[P]].  Ranges are cut where the hash density (leading bits = outer
+ * bases of the canonical k-mer) predicts equal posting counts.  *overflow != 0: the piece does not fit the block
+ * (or the shared-memory bucket sort does not apply); the block header then says so to every rank.
+ * *used_words = 5 + 2U + P: only that prefix of the block needs to travel (exchange the sizes first and gather
+ * blocks of the largest one; kssd_b200_index_adopt_parts takes that smaller stride). */
+int kssd_b200_index_build_range(kssd_ctx *ctx, const uint32_t *d_hashes, const uint64_t *d_genome_off,
+                                uint32_t n_genomes, uint32_t part, uint32_t parts, uint32_t *d_block,
+                                uint64_t block_words, uint64_t *used_words, int *overflow);
+/* Adopts the exchanged pieces (`parts` blocks of block_words u32 in device memory, hash ranges ascending) as this
+ * context's index: concatenated CSR, lookup directory, reference sizes from d_genome_off.  *overflow != 0: some
+ * rank reported overflow -- identical on every rank; call kssd_b200_index_build on the full input instead. */
+int kssd_b200_index_adopt_parts(kssd_ctx *ctx, const uint32_t *d_blocks, uint64_t block_words, uint32_t parts,
+                                const uint64_t *d_genome_off, uint32_t n_genomes, int *overflow);
 /* Device views of the CSR index (for replication to other GPUs with one NCCL broadcast). */
 int kssd_b200_index_device_views(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, uint32_t *n_ref,
                                  const uint32_t **d_uniq_hash, const uint64_t **d_uniq_off,

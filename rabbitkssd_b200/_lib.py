@@ -48,6 +48,9 @@ SYMBOLS = {
     "kssd_b200_sketch_concat_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p),
                                                  C.POINTER(C.c_void_p), u64p, C.POINTER(C.c_int)]),
     "kssd_b200_index_build": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]),
+    "kssd_b200_index_build_range": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint64,
+                                              u64p, C.POINTER(C.c_int)]),
+    "kssd_b200_index_adopt_parts": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_int)]),
     "kssd_b200_index_export": (C.c_int, [C.c_void_p, u64p, u64p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p)]),
     "kssd_b200_index_load": (C.c_int, [C.c_void_p, C.c_uint64, u32p, u32p, C.c_uint64, u32p, C.c_uint32]),
     "kssd_b200_index_device_views": (C.c_int, [C.c_void_p, u64p, u64p, u32p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),

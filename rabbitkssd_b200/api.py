@@ -164,6 +164,19 @@ class Context:
     def index_build_device(self, d_hashes, d_genome_off, n_genomes):
         check(self.lib.kssd_b200_index_build(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1))
 
+    def index_build_range(self, d_hashes, d_genome_off, n_genomes, part, parts, d_block, block_words):
+        """CSR of hash range `part` of `parts` packed into the caller's device block -> (overflow flag, words used)."""
+        ov, used = C.c_int(), C.c_uint64()
+        check(self.lib.kssd_b200_index_build_range(self.h, d_hashes, d_genome_off, n_genomes, part, parts, d_block, block_words,
+                                                   C.byref(used), C.byref(ov)))
+        return bool(ov.value), used.value
+
+    def index_adopt_parts(self, d_blocks, block_words, parts, d_genome_off, n_genomes):
+        """Exchanged pieces -> this context's index; -> overflow flag (some rank's piece did not fit)."""
+        ov = C.c_int()
+        check(self.lib.kssd_b200_index_adopt_parts(self.h, d_blocks, block_words, parts, d_genome_off, n_genomes, C.byref(ov)))
+        return bool(ov.value)
+
     def index_export(self):
         """-> (uniq_hash u32[U], uniq_count u32[U], dict u32[P])"""
         U, P = C.c_uint64(), C.c_uint64()

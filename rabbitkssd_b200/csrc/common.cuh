@@ -154,6 +154,10 @@ int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_ge
 // index.cu
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
                        uint64_t total);
+int index_build_range(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total, uint32_t part,
+                      uint32_t parts, uint32_t *d_block, uint64_t block_words, uint64_t *used_words, int *overflow);
+int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_words, uint32_t parts, const uint64_t *d_genome_off, uint32_t n_genomes,
+                      int *overflow);
 int index_build_buckets(kssd_ctx *c, int64_t known_max_hash = -1);  // after d_uniq_hash / n_uniq are in place
 // dist.cu
 int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,

@@ -4,6 +4,7 @@
 // stable radix sort on the hash bits (input is genome-major, so ids stay ascending inside a posting list,
 // matching the reference's push_back order sketch.cpp:979-985), then head detection + scan for the CSR.
 #include <algorithm>
+#include <cmath>
 
 #include "common.cuh"
 
@@ -129,21 +130,27 @@ int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
 static constexpr uint32_t kBucketCapSmall = 2048, kBucketCapLarge = 8192;  // pairs per bucket: 16 KB / 64 KB of shared memory
 static constexpr uint32_t kSubBuckets = 1024;                               // counting-sort buckets inside a bucket
 
+// Both passes can be restricted to the hashes in [h_lo, h_last] (multi-GPU: every rank builds the CSR of one hash range,
+// index_build_range); buckets are then relative to h_lo.
 __global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, uint64_t total, int shift, uint32_t last_bucket,
-                                                          uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
+                                                          uint32_t h_lo, uint32_t h_last, uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < total) rank[i] = atomicAdd(bcount + min(hashes[i] >> shift, last_bucket), 1u);  // arrival order inside the bucket
+    if (i >= total) return;
+    const uint32_t h = hashes[i];
+    if (h < h_lo || h > h_last) return;
+    rank[i] = atomicAdd(bcount + min((h - h_lo) >> shift, last_bucket), 1u);  // arrival order inside the bucket
 }
 
 // grid = (genomes, chunks): the genome id is blockIdx.x; the slot inside the bucket was drawn by the histogram pass
 __global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
-                                                          uint32_t last_bucket, const uint64_t *__restrict__ bstart, const uint32_t *__restrict__ rank,
-                                                          uint64_t *__restrict__ pairs) {
+                                                          uint32_t last_bucket, uint32_t h_lo, uint32_t h_last, const uint64_t *__restrict__ bstart,
+                                                          const uint32_t *__restrict__ rank, uint64_t *__restrict__ pairs) {
     const uint32_t g = blockIdx.x;
     const uint64_t e1 = genome_off[g + 1];
     for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
         const uint32_t h = hashes[e];
-        const uint32_t b = min(h >> shift, last_bucket);
+        if (h < h_lo || h > h_last) continue;
+        const uint32_t b = min((h - h_lo) >> shift, last_bucket);
         pairs[bstart[b] + rank[e]] = ((uint64_t)h << 32) | g;
     }
 }
@@ -151,7 +158,7 @@ __global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__rest
 // One CTA per bucket.  Writes the postings of the bucket (dict), its distinct hashes + list starts (compacted at the
 // head of the bucket's range of tmp_hash / tmp_rel), their number, and folds the largest hash into *max_hash.
 __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart, int shift,
-                                                          uint32_t cap, uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash,
+                                                          uint32_t h_lo, uint32_t cap, uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash,
                                                           uint32_t *__restrict__ tmp_rel, uint32_t *__restrict__ hcount,
                                                           uint32_t *__restrict__ flags /* [0] overflow, [1] max hash */) {
     extern __shared__ uint64_t s_pairs[];
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__rest
         const int sub_shift = shift > 10 ? shift - 10 : 0;
         const uint32_t first = (uint32_t)(((uint64_t)b << shift) >> sub_shift);
         count_sort_smem<uint64_t>(pairs + b0, s_pairs, reinterpret_cast<uint32_t *>(s_pairs + cap), n, kSubBuckets,
-                                  [=](uint64_t k) { return min(((uint32_t)(k >> 32) >> sub_shift) - first, kSubBuckets - 1); });
+                                  [=](uint64_t k) { return min((((uint32_t)(k >> 32) - h_lo) >> sub_shift) - first, kSubBuckets - 1); });
     }
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (uint32_t c0 = 0; c0 < n; c0 += blockDim.x) {
@@ -207,7 +214,7 @@ __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__rest
 
 __global__ void __launch_bounds__(128) bucket_pack_kernel(const uint64_t *__restrict__ bstart, const uint64_t *__restrict__ hstart,
                                                           const uint32_t *__restrict__ tmp_hash, const uint32_t *__restrict__ tmp_rel,
-                                                          uint32_t n_buckets, uint64_t total, uint32_t *__restrict__ uniq_hash,
+                                                          uint32_t n_buckets, uint32_t *__restrict__ uniq_hash,
                                                           uint64_t *__restrict__ uniq_off) {
     const uint32_t b = blockIdx.x;
     const uint64_t b0 = bstart[b], u0 = hstart[b];
@@ -216,20 +223,23 @@ __global__ void __launch_bounds__(128) bucket_pack_kernel(const uint64_t *__rest
         uniq_hash[u0 + j] = tmp_hash[b0 + j];
         uniq_off[u0 + j] = b0 + tmp_rel[b0 + j];
     }
-    if (b == n_buckets - 1 && threadIdx.x == 0) uniq_off[hstart[n_buckets]] = total;
+    if (b == n_buckets - 1 && threadIdx.x == 0) uniq_off[hstart[n_buckets]] = bstart[n_buckets];
 }
 
 __global__ void segment_scan_kernel(const uint32_t *counts, uint32_t n, uint64_t *start, uint32_t *max_out);  // segsort.cu
 
 // Returns KSSD_OK with *done = false when a bucket overflowed (caller falls back to the radix path).
+// [h_lo, h_last]: the hash range to index (0 .. 0xFFFFFFFF = everything); range_bits = bits of (h_last - h_lo) the
+// buckets are cut from; expect = postings expected in the range (sizes the buckets); *n_post = postings found.
 static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total,
-                                int hash_bits, uint32_t *d_max_size, bool *done, uint64_t *n_uniq, uint32_t *max_hash) {
+                                uint32_t h_lo, uint32_t h_last, int range_bits, uint64_t expect, uint32_t *d_max_size, bool *done,
+                                uint64_t *n_uniq, uint64_t *n_post, uint32_t *max_hash) {
     cudaStream_t st = c->stream;
     *done = false;
     int B = 0;
-    while (B < 18 && (total >> (B + 10)) > 0) B++;  // ~1 k pairs per bucket on average
-    if (B > hash_bits) B = hash_bits;
-    const int shift = hash_bits - B;
+    while (B < 18 && (expect >> (B + 10)) > 0) B++;  // ~1 k pairs per bucket on average
+    if (B > range_bits) B = range_bits;
+    const int shift = range_bits - B;
     const uint32_t nb = 1u << B;
     // scratch: [bstart nb+1][hstart nb+1] u64, then [bcount nb][bcur nb][hcount nb][flags 4] u32
     KSSD_TRY(c->d_sort_counts.reserve(((uint64_t)nb + 1) * 16 + (uint64_t)nb * 12 + 16, st));
@@ -242,9 +252,11 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     uint32_t *tmp_rel = tmp_hash + total;
     const uint64_t avg_len = total / n_genomes + 1;
     const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);
-    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, bcount, tmp_hash /* rank, dead before the sort */);
+    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, h_lo, h_last, bcount,
+                                                                       tmp_hash /* rank, dead before the sort */);
     segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
-    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, bstart, tmp_hash, c->d_pairs.as<uint64_t>());
+    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, h_last, bstart, tmp_hash,
+                                                                c->d_pairs.as<uint64_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
     static bool attr_done = false;
@@ -258,23 +270,174 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     // small shared-memory footprint first (more CTAs per SM); one retry with the large one when a bucket overflowed
     for (uint32_t cap : {kBucketCapSmall, kBucketCapLarge}) {
         KSSD_CUDA(cudaMemsetAsync(flags, 0, 16, st));
-        bucket_sort_kernel<<<nb, 256, (size_t)cap * 8 + kSubBuckets * 4, st>>>(c->d_pairs.as<uint64_t>(), bstart, shift, cap, c->d_dict.as<uint32_t>(),
+        bucket_sort_kernel<<<nb, 256, (size_t)cap * 8 + kSubBuckets * 4, st>>>(c->d_pairs.as<uint64_t>(), bstart, shift, h_lo, cap, c->d_dict.as<uint32_t>(),
                                                                                tmp_hash, tmp_rel, hcount, flags);
         segment_scan_kernel<<<1, 1024, 0, st>>>(hcount, nb, hstart, nullptr);
-        bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, total, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
+        bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
         KSSD_CUDA(cudaGetLastError());
         c->launches += 3;
         KSSD_CUDA(cudaMemcpyAsync(hs, hstart + nb, 8, cudaMemcpyDeviceToHost, st));
         KSSD_CUDA(cudaMemcpyAsync(hs + 1, flags, 8, cudaMemcpyDeviceToHost, st));
         KSSD_CUDA(cudaMemcpyAsync(hs + 2, d_max_size, 4, cudaMemcpyDeviceToHost, st));
+        KSSD_CUDA(cudaMemcpyAsync(hs + 3, bstart + nb, 8, cudaMemcpyDeviceToHost, st));
         KSSD_CUDA(cudaStreamSynchronize(st));
         c->max_ref_size = *reinterpret_cast<const uint32_t *>(hs + 2);
         if (!fl[0]) break;
     }
     if (fl[0]) return KSSD_OK;  // a bucket does not fit shared memory: caller takes the radix path
     *n_uniq = hs[0];
+    *n_post = hs[3];
     *max_hash = fl[1];
     *done = true;
+    return KSSD_OK;
+}
+
+static int index_scratch(kssd_ctx *c, uint32_t n_genomes, uint64_t total, const uint64_t *d_genome_off, uint32_t **d_max) {
+    cudaStream_t st = c->stream;
+    KSSD_TRY(c->d_ref_sizes.reserve((uint64_t)(n_genomes + 2) * 4, st));
+    *d_max = c->d_ref_sizes.as<uint32_t>() + n_genomes;
+    KSSD_CUDA(cudaMemsetAsync(*d_max, 0, 4, st));
+    if (n_genomes) {
+        ref_sizes_kernel<<<(n_genomes + 255) / 256, 256, 0, st>>>(d_genome_off, n_genomes, c->d_ref_sizes.as<uint32_t>(), *d_max);
+        c->launches++;
+    }
+    KSSD_TRY(c->d_pairs.reserve(std::max<uint64_t>(total, 1) * 8, st));
+    KSSD_TRY(c->d_pairs_tmp.reserve(std::max<uint64_t>(total, 1) * 8, st));
+    KSSD_TRY(c->d_dict.reserve(std::max<uint64_t>(total, 1) * 4, st));
+    KSSD_TRY(c->d_uniq_hash.reserve(std::max<uint64_t>(total, 1) * 4, st));
+    KSSD_TRY(c->d_uniq_off.reserve((total + 1) * 8, st));
+    return KSSD_OK;
+}
+
+// ---- multi-GPU: one hash range per rank, the pieces are exchanged and adopted ---------------------------------
+// Hash range of part p of `parts`: the leading hash bits are the outer bases of the CANONICAL k-mer (the smaller of
+// the two strands, src/sketch.cpp:508), so their density falls linearly, F(x) = 2x - x^2; the boundaries
+// x_p = 1 - sqrt(1 - p/parts) give every part the same expected number of postings.
+static uint32_t range_begin(int hash_bits, uint32_t part, uint32_t parts) {
+    if (part == 0) return 0;
+    const double x = 1.0 - sqrt(1.0 - (double)part / (double)parts);
+    const double span = hash_bits >= 32 ? 4294967296.0 : (double)(1ull << hash_bits);
+    const double v = floor(x * span);
+    return v >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)v;
+}
+
+// block layout (u32 words): [0] distinct hashes U, [1] postings P, [2] max hash, [3] reserved, then uniq_hash[U],
+// list starts relative to the piece [U + 1], postings [P].
+__global__ void __launch_bounds__(256) piece_pack_kernel(const uint32_t *__restrict__ uniq_hash, const uint64_t *__restrict__ uniq_off,
+                                                         const uint32_t *__restrict__ dict, uint32_t U, uint32_t P, uint32_t max_hash,
+                                                         uint32_t *__restrict__ block) {
+    const uint64_t n = 4ull + U + (U + 1ull) + P;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t v;
+        if (i < 4) v = i == 0 ? U : i == 1 ? P : i == 2 ? max_hash : 0u;
+        else if (i < 4ull + U) v = uniq_hash[i - 4];
+        else if (i < 5ull + 2ull * U) v = (uint32_t)uniq_off[i - 4 - U];
+        else v = dict[i - 5 - 2ull * U];
+        block[i] = v;
+    }
+}
+
+int index_build_range(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total, uint32_t part,
+                      uint32_t parts, uint32_t *d_block, uint64_t block_words, uint64_t *used_words, int *overflow) {
+    cudaStream_t st = c->stream;
+    *overflow = 0;
+    *used_words = 0;
+    if (block_words < 8) { set_error("index_build_range: block too small"); return KSSD_E_ARG; }
+    if (total >= (1ull << 32) || n_genomes == 0) {
+        *overflow = 1;
+        KSSD_CUDA(cudaMemsetAsync(d_block, 0xFF, 16, st));
+        return KSSD_OK;
+    }
+    uint32_t *d_max;
+    KSSD_TRY(index_scratch(c, n_genomes, total, d_genome_off, &d_max));
+    int hash_bits = c->have_params ? 4 * (c->sp.half_k - c->sp.drlevel) : 32;
+    if (hash_bits > 32) hash_bits = 32;
+    const uint32_t h_lo = range_begin(hash_bits, part, parts);
+    const uint32_t h_last = part + 1 == parts ? 0xFFFFFFFFu : range_begin(hash_bits, part + 1, parts) - 1u;
+    uint64_t U = 0, P = 0;
+    uint32_t mh = 0;
+    bool done = false;
+    if (total && h_last >= h_lo) {
+        const uint64_t width = part + 1 == parts ? (1ull << hash_bits) - std::min<uint64_t>(h_lo, 1ull << hash_bits) : (uint64_t)h_last - h_lo + 1;
+        int range_bits = 1;
+        while (range_bits < 32 && (1ull << range_bits) < width) range_bits++;
+        KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, h_lo, h_last, range_bits, total / parts + 1, d_max, &done, &U,
+                                      &P, &mh));
+        if (!done) *overflow = 1;  // heavily skewed hashes: callers build the whole index on every rank instead
+    }
+    if (5ull + 2 * U + P > block_words) *overflow = 1;
+    if (*overflow) {  // header 0xFFFFFFFF...: every rank sees it after the exchange (index_adopt_parts reports it)
+        KSSD_CUDA(cudaMemsetAsync(d_block, 0xFF, 16, st));
+        return KSSD_OK;
+    }
+    *used_words = 5ull + 2 * U + P;
+    if (U == 0) KSSD_CUDA(cudaMemsetAsync(c->d_uniq_off.p, 0, 8, st));
+    piece_pack_kernel<<<(unsigned)std::min<uint64_t>((5ull + 2 * U + P + 255) / 256, 148 * 16), 256, 0, st>>>(
+        c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>(), c->d_dict.as<uint32_t>(), (uint32_t)U, (uint32_t)P, mh, d_block);
+    KSSD_CUDA(cudaGetLastError());
+    c->launches++;
+    return KSSD_OK;
+}
+
+// pieces (parts blocks of block_words u32, hash ranges ascending) -> the ctx's CSR: one CTA row per piece
+__global__ void __launch_bounds__(256) piece_adopt_kernel(const uint32_t *__restrict__ blocks, uint64_t block_words,
+                                                          const uint64_t *__restrict__ base /* [2 * parts]: distinct-hash base, posting base */,
+                                                          uint32_t *__restrict__ uniq_hash, uint64_t *__restrict__ uniq_off, uint32_t *__restrict__ dict) {
+    const uint32_t r = blockIdx.y;
+    const uint32_t *blk = blocks + (uint64_t)r * block_words;
+    const uint32_t U = blk[0], P = blk[1];
+    const uint64_t ub = base[2 * r], pb = base[2 * r + 1];
+    const uint64_t n = (uint64_t)U + P;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        if (i < U) {
+            uniq_hash[ub + i] = blk[4 + i];
+            uniq_off[ub + i] = pb + blk[4 + U + i];
+        } else {
+            dict[pb + (i - U)] = blk[5 + 2ull * U + (i - U)];
+        }
+    }
+}
+
+int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_words, uint32_t parts, const uint64_t *d_genome_off, uint32_t n_genomes,
+                      int *overflow) {
+    cudaStream_t st = c->stream;
+    *overflow = 0;
+    c->have_index = false;
+    if (parts == 0 || parts > 64) { set_error("index_adopt_parts: 1..64 parts"); return KSSD_E_ARG; }
+    KSSD_TRY(c->h_scalar.reserve(64 * 16 + 64));
+    uint32_t *hd = c->h_scalar.as<uint32_t>();  // 4 header words per part
+    KSSD_CUDA(cudaMemcpy2DAsync(hd, 16, d_blocks, block_words * 4, 16, parts, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaStreamSynchronize(st));
+    uint64_t base[128];
+    uint64_t U = 0, P = 0;
+    uint32_t mh = 0;
+    for (uint32_t r = 0; r < parts; r++) {
+        const uint64_t u = hd[4 * r], p = hd[4 * r + 1];
+        if (5ull + 2 * u + p > block_words) { *overflow = 1; return KSSD_OK; }  // the piece's rank reported overflow (header left as it was) or a bad block
+        base[2 * r] = U;
+        base[2 * r + 1] = P;
+        U += u;
+        P += p;
+        if (u) mh = std::max(mh, hd[4 * r + 2]);
+    }
+    uint32_t *d_max;
+    KSSD_TRY(index_scratch(c, n_genomes, P, d_genome_off, &d_max));
+    KSSD_TRY(c->d_sort_counts.reserve(128 * 8, st));
+    KSSD_CUDA(cudaMemcpyAsync(c->d_sort_counts.p, base, (size_t)parts * 16, cudaMemcpyHostToDevice, st));
+    if (U + P) {
+        piece_adopt_kernel<<<dim3(148 * 2, parts), 256, 0, st>>>(d_blocks, block_words, c->d_sort_counts.as<uint64_t>(), c->d_uniq_hash.as<uint32_t>(),
+                                                                 c->d_uniq_off.as<uint64_t>(), c->d_dict.as<uint32_t>());
+        c->launches++;
+    }
+    KSSD_CUDA(cudaMemcpyAsync(c->d_uniq_off.as<uint64_t>() + U, &P, 8, cudaMemcpyHostToDevice, st));  // P lives on this frame: synchronise below
+    KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, d_max, 4, cudaMemcpyDeviceToHost, st));
+    KSSD_CUDA(cudaStreamSynchronize(st));
+    c->max_ref_size = *c->h_scalar.as<uint32_t>();
+    c->n_ref = n_genomes;
+    c->n_post = P;
+    c->n_uniq = U;
+    KSSD_TRY(index_build_buckets(c, U ? (int64_t)mh : -1));
+    c->have_index = true;
     return KSSD_OK;
 }
 
@@ -283,18 +446,8 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
     c->have_index = false;
     c->n_ref = n_genomes;
     c->n_post = total;
-    KSSD_TRY(c->d_ref_sizes.reserve((uint64_t)(n_genomes + 2) * 4, st));
-    uint32_t *d_max = c->d_ref_sizes.as<uint32_t>() + n_genomes;
-    KSSD_CUDA(cudaMemsetAsync(d_max, 0, 4, st));
-    if (n_genomes) {
-        ref_sizes_kernel<<<(n_genomes + 255) / 256, 256, 0, st>>>(d_genome_off, n_genomes, c->d_ref_sizes.as<uint32_t>(), d_max);
-        c->launches++;
-    }
-    KSSD_TRY(c->d_pairs.reserve(std::max<uint64_t>(total, 1) * 8, st));
-    KSSD_TRY(c->d_pairs_tmp.reserve(std::max<uint64_t>(total, 1) * 8, st));
-    KSSD_TRY(c->d_dict.reserve(std::max<uint64_t>(total, 1) * 4, st));
-    KSSD_TRY(c->d_uniq_hash.reserve(std::max<uint64_t>(total, 1) * 4, st));
-    KSSD_TRY(c->d_uniq_off.reserve((total + 1) * 8, st));
+    uint32_t *d_max;
+    KSSD_TRY(index_scratch(c, n_genomes, total, d_genome_off, &d_max));
     uint64_t n_uniq = 0;
     int64_t known_max = -1;
     bool done = false;
@@ -302,7 +455,8 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
     if (hash_bits > 32) hash_bits = 32;
     if (total && n_genomes && !c->force_radix && total < (1ull << 32)) {
         uint32_t mh = 0;
-        KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, hash_bits, d_max, &done, &n_uniq, &mh));
+        uint64_t n_post = 0;
+        KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, 0u, 0xFFFFFFFFu, hash_bits, total, d_max, &done, &n_uniq, &n_post, &mh));
         if (done) known_max = mh;
     }
     if (done) {

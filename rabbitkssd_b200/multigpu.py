@@ -62,6 +62,30 @@ def gather_sketches_device(dist, ctx, hashes_local, sizes_local, world, cap):
     return ph, po, total  # the concat call synchronised the stream: recv may be freed
 
 
+def build_index_sharded(dist, ctx, d_hashes, d_genome_off, n_genomes, total, rank, world):
+    """Index build sharded by hash range + all-gather of the pieces over NCCL (north_star: "the reference index
+    replicated by NCCL over NVLink"): rank r builds the CSR of hash range r from the sketches of all genomes
+    (kssd_b200_index_build_range, ~1/world of the replicated build), the piece sizes are exchanged, blocks of the
+    largest size are all-gathered and every rank adopts them (kssd_b200_index_adopt_parts).  Returns False when a
+    piece could not be built -- the same answer on every rank -- and the caller builds the whole index locally
+    (ctx.index_build_device)."""
+    # a piece holds P ~ total/world postings and U <= P distinct hashes: 5 + 2U + P words; generous local capacity
+    cap_words = 3 * (2 * (total // world) + 1024) + 8
+    dev = torch.device("cuda", torch.cuda.current_device())
+    send = torch.empty(cap_words, dtype=torch.int32, device=dev)
+    overflow, used = ctx.index_build_range(d_hashes, d_genome_off, n_genomes, rank, world, send.data_ptr(), cap_words)
+    mine = torch.tensor([-1 if overflow else used], dtype=torch.int64).to(dev, non_blocking=True)
+    sizes = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(sizes, mine)
+    sizes = sizes.cpu()
+    if int(sizes.min()) < 0:
+        return False
+    block_words = min(cap_words, (int(sizes.max()) + 1023) // 1024 * 1024)
+    recv = torch.empty(world * block_words, dtype=torch.int32, device=dev)
+    dist.all_gather_into_tensor(recv, send[:block_words])
+    return not ctx.index_adopt_parts(recv.data_ptr(), block_words, world, d_genome_off, n_genomes)
+
+
 def gather_sketches(dist, hashes_local, sizes_local, world):
     """All-gather of CSR sketch shards.  hashes_local: int32[total_local] (the u32 hashes, bit-cast), sizes_local:
     int64[n_local] per-genome sketch sizes; every rank holds the same number of genomes.  Returns

@@ -256,3 +256,51 @@ def test_sketch_concat_device_matches_numpy():
         assert overflow
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("parts", [1, 2, 3, 8])
+def test_index_sharded_by_hash_range_equals_full_build(parts):
+    """Multi-GPU index path on one GPU: every hash-range piece (kssd_b200_index_build_range) packed into its block, the
+    blocks adopted (kssd_b200_index_adopt_parts) -> the same CSR as the full build, and the same alldist hits."""
+    import torch
+    k, s, l = 10, 6, 3
+    fams = [g for f in range(6) for g in synth.family(100 + f, 5, 120000, 0.03, n_contigs=2)]
+    c = api.Context(0)
+    try:
+        c.set_params(k, s, l, util.shuffled_dim(k, s, l))
+        seq, _, off = synth.pack_batch(fams)
+        h, goff = c.sketch(seq, off)
+        n = len(fams)
+        c.index_build(h, goff)
+        want = [np.array(x, copy=True) for x in c.index_export()]
+        want_hits = c.dist_rows(h, goff, True, 2 * k, 0.2)
+        d_h = torch.from_numpy(h.view(np.int32)).cuda()
+        d_o = torch.from_numpy(goff.astype(np.int64)).cuda()
+        cap = 3 * len(h) + 64
+        blocks = torch.zeros(parts * cap, dtype=torch.int32, device="cuda")
+        used_all = []
+        for p in range(parts):
+            ov, used = c.index_build_range(d_h.data_ptr(), d_o.data_ptr(), n, p, parts, blocks.data_ptr() + p * cap * 4, cap)
+            assert not ov and 5 <= used <= cap
+            used_all.append(used)
+        # the pieces hold comparable numbers of postings (ranges follow the hash density)
+        posts = [int(blocks[p * cap + 1]) for p in range(parts)]
+        assert sum(posts) == len(h)
+        if parts > 1:
+            assert max(posts) < 1.5 * len(h) / parts
+        # ship only the used prefix, as the all-gather does
+        stride = (max(used_all) + 1023) // 1024 * 1024
+        packed = torch.cat([blocks[p * cap:p * cap + stride] for p in range(parts)]) if stride <= cap else blocks
+        assert not c.index_adopt_parts(packed.data_ptr(), min(stride, cap), parts, d_o.data_ptr(), n)
+        got = c.index_export()
+        for a, b in zip(got, want):
+            assert np.array_equal(np.asarray(a), np.asarray(b))
+        hits = c.dist_rows(h, goff, True, 2 * k, 0.2)
+        key = lambda x: x[np.lexsort((x[:, 2], x[:, 1], x[:, 0]))]
+        assert np.array_equal(key(np.asarray(hits)), key(np.asarray(want_hits)))
+        # a block that is too small reports overflow, and adopting it reports overflow too
+        small = torch.zeros(16, dtype=torch.int32, device="cuda")
+        ov, _ = c.index_build_range(d_h.data_ptr(), d_o.data_ptr(), n, 0, 1, small.data_ptr(), 16)
+        assert ov and c.index_adopt_parts(small.data_ptr(), 16, 1, d_o.data_ptr(), n)
+    finally:
+        c.close()
