@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--family", type=int, default=10)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--index-sharded", action="store_true", help="N > 1: build the index sharded by hash range and all-gather the pieces")
     ap.add_argument("--phases", action="store_true", help="diagnostic: per-phase wall times (synchronised) on stderr after the timed runs")
     ap.add_argument("--cpu-sample-genomes", type=int, default=256)
     return ap.parse_args()
@@ -308,7 +309,10 @@ def run_b200(args):
         else:
             ph, po = d_h, d_o
         t0 = mark("gather", t0)
-        if world == 1 or not build_index_sharded(dist, ctx, ph, po, n_total, state["total_all"], rank, world):
+        # every rank builds the whole index from the gathered sketches (0.69 ms for 12.2 M postings); the build sharded by
+        # hash range + all-gather of the pieces (--index-sharded) measured the same at 4 GPUs (profiles/r01u): its
+        # fixed costs (two more collectives, adopt pass) eat what the smaller sort saves
+        if world == 1 or not args.index_sharded or not build_index_sharded(dist, ctx, ph, po, n_total, state["total_all"], rank, world):
             ctx.index_build_device(ph, po, n_total)
         t0 = mark("index", t0)
         d_hits, n_hits = ctx.dist_rows_device(ph, po, n_total, True, 2 * K, MAX_DIST, 0, rows=(r0, r1))
@@ -364,6 +368,9 @@ def run_b200(args):
             step_device()
         state["diag"] = False
         sys.stderr.write("phases rank %d (ms/step, synchronised): %s\n" % (rank, json.dumps({k: round(v / 3, 3) for k, v in phase_t.items()})))
+        from rabbitkssd_b200 import multigpu as _mg
+        if _mg.TRACE:
+            sys.stderr.write("multigpu trace rank %d (median ms per call, synchronised): %s\n" % (rank, json.dumps({k: round(sorted(v)[len(v) // 2], 3) for k, v in _mg.TRACE.items() if k})))
 
     # ---- end to end: pinned host buffers -> C-ABI (H2D inside the timed region) -> hits read back ----
     host = torch.empty(n_bytes, dtype=torch.uint8, pin_memory=True)

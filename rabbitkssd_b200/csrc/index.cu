@@ -127,7 +127,8 @@ int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
 // on the full (hash << 32 | genome) key, which also gives the ascending genome ids inside a posting list
 // (the reference's push_back order, sketch.cpp:979-985).  ~50 B of HBM traffic per posting instead of the
 // 4 radix passes x 48 B of the device-wide sort below (kept for bucket overflow, i.e. heavily skewed hashes).
-static constexpr uint32_t kBucketCapSmall = 2048, kBucketCapLarge = 8192;  // pairs per bucket: 16 KB / 64 KB of shared memory
+static constexpr uint32_t kBucketCapSmall = 3072, kBucketCapLarge = 8192;  // pairs per bucket: 24 KB / 64 KB of shared memory; the hash density falls
+                                                                           // linearly (see range_begin), so the first buckets hold 2 x the mean of ~750-1000
 static constexpr uint32_t kSubBuckets = 1024;                               // counting-sort buckets inside a bucket
 
 // Both passes can be restricted to the hashes in [h_lo, h_last] (multi-GPU: every rank builds the CSR of one hash range,

@@ -4,7 +4,22 @@ The distance path shards by query rows with a replicated index (src/dist.cpp:174
 state), so the only exchange is the all-gather of the per-rank sketch shards before the index is built.  Everything
 here is plain torch on whatever device the tensors live on, so the same code runs under NCCL on B200s and under
 gloo on CPUs (tests/test_multirank_gloo.py)."""
+import os
+import time
+
 import torch
+
+# diagnostic: KSSD_MG_TRACE=1 -> every sub-step is followed by a device synchronize and its wall time accumulated here
+TRACE = {} if os.environ.get("KSSD_MG_TRACE") else None
+
+
+def _tick(name, t0):
+    if TRACE is None:
+        return t0
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    TRACE.setdefault(name, []).append((t1 - t0) * 1e3)
+    return t1
 
 
 def triangle_bounds(n, parts, row_cost=0.0):
@@ -51,12 +66,16 @@ def gather_sketches_device(dist, ctx, hashes_local, sizes_local, world, cap):
     n_local = sizes_local.numel()
     tot = hashes_local.numel()
     dev = hashes_local.device
+    t0 = _tick("", time.perf_counter()) if TRACE is not None else 0.0
     send = torch.empty(n_local + cap, dtype=torch.int32, device=dev)
     send[:n_local] = sizes_local.to(torch.int32)
     send[n_local:n_local + min(tot, cap)] = hashes_local[:cap]
     recv = torch.empty(world * (n_local + cap), dtype=torch.int32, device=dev)
+    t0 = _tick("gather.pack", t0)
     dist.all_gather_into_tensor(recv, send)
+    t0 = _tick("gather.nccl", t0)
     ph, po, total, overflow = ctx.sketch_concat_device(recv.data_ptr(), n_local + cap, n_local, world)
+    t0 = _tick("gather.concat", t0)
     if overflow:
         return None
     return ph, po, total  # the concat call synchronised the stream: recv may be freed
@@ -72,18 +91,24 @@ def build_index_sharded(dist, ctx, d_hashes, d_genome_off, n_genomes, total, ran
     # a piece holds P ~ total/world postings and U <= P distinct hashes: 5 + 2U + P words; generous local capacity
     cap_words = 3 * (2 * (total // world) + 1024) + 8
     dev = torch.device("cuda", torch.cuda.current_device())
+    t0 = _tick("", time.perf_counter()) if TRACE is not None else 0.0
     send = torch.empty(cap_words, dtype=torch.int32, device=dev)
     overflow, used = ctx.index_build_range(d_hashes, d_genome_off, n_genomes, rank, world, send.data_ptr(), cap_words)
+    t0 = _tick("index.build_range", t0)
     mine = torch.tensor([-1 if overflow else used], dtype=torch.int64).to(dev, non_blocking=True)
     sizes = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(sizes, mine)
     sizes = sizes.cpu()
+    t0 = _tick("index.sizes", t0)
     if int(sizes.min()) < 0:
         return False
     block_words = min(cap_words, (int(sizes.max()) + 1023) // 1024 * 1024)
     recv = torch.empty(world * block_words, dtype=torch.int32, device=dev)
     dist.all_gather_into_tensor(recv, send[:block_words])
-    return not ctx.index_adopt_parts(recv.data_ptr(), block_words, world, d_genome_off, n_genomes)
+    t0 = _tick("index.nccl", t0)
+    ok = not ctx.index_adopt_parts(recv.data_ptr(), block_words, world, d_genome_off, n_genomes)
+    _tick("index.adopt", t0)
+    return ok
 
 
 def gather_sketches(dist, hashes_local, sizes_local, world):
