@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--family", type=int, default=10)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nccl-gather", action="store_true", help="N > 1: gather the sketch shards with one NCCL all-gather instead of peer-memory reads")
     ap.add_argument("--index-sharded", action="store_true", help="N > 1: build the index sharded by hash range and all-gather the pieces")
     ap.add_argument("--phases", action="store_true", help="diagnostic: per-phase wall times (synchronised) on stderr after the timed runs")
     ap.add_argument("--cpu-sample-genomes", type=int, default=256)
@@ -239,7 +240,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from rabbitkssd_b200 import api
-    from rabbitkssd_b200.multigpu import build_index_sharded, gather_sketches, gather_sketches_device, triangle_bounds
+    from rabbitkssd_b200.multigpu import PeerGather, build_index_sharded, gather_sketches, gather_sketches_device, triangle_bounds
     import oracle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -278,6 +279,8 @@ def run_b200(args):
     bounds = triangle_bounds(n_total, world, row_cost=5.0 * sk_size)
     r0, r1 = bounds[rank], bounds[rank + 1]
     state = {}
+    if world > 1 and not args.nccl_gather:
+        state["peers"] = PeerGather(dist, ctx, n_local, gather_cap, rank, world)
 
     phase_t = {}
 
@@ -296,13 +299,14 @@ def run_b200(args):
             raise RuntimeError(f"rank {rank}: sketch size changed between steps: {state['tot0']} -> {tot}")
         t0 = mark("sort_unique", t0)
         if world > 1:
-            h_loc = dev_tensor(torch, d_h, tot, torch.int32)
-            o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
-            got = gather_sketches_device(dist, ctx, h_loc, o_loc[1:] - o_loc[:-1], world, gather_cap)
+            def shard():
+                o_loc = dev_tensor(torch, d_o, n_local + 1, torch.int64)
+                return dev_tensor(torch, d_h, tot, torch.int32), o_loc[1:] - o_loc[:-1]
+            got = state["peers"].gather() if not args.nccl_gather else gather_sketches_device(dist, ctx, *shard(), world, gather_cap)
             if got is not None:
                 ph, po, state["total_all"] = got
             else:  # some rank's shard exceeded the agreed block size: two-step gather with exact sizes
-                hashes, off = gather_sketches(dist, h_loc, o_loc[1:] - o_loc[:-1], world)
+                hashes, off = gather_sketches(dist, *shard(), world)
                 ph, po = hashes.data_ptr(), off.data_ptr()
                 state["keep"] = (hashes, off)
                 state["total_all"] = hashes.numel()

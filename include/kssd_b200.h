@@ -109,6 +109,22 @@ int kssd_b200_sketch_concat_device(kssd_ctx *ctx, const uint32_t *d_parts, uint6
                                    uint32_t world, const uint32_t **d_hashes, const uint64_t **d_genome_off,
                                    uint64_t *total, int *overflow);
 
+/* Gather over PEER MEMORY (NVLink, CUDA IPC) instead of a collective: every rank keeps its shard in two buffers of
+ * its own (double buffered), mapped into all ranks of the node; gathering is then the concat kernels reading the
+ * peers' buffers in place -- one pass of peer loads, no NCCL transfer, no staging copy.
+ *   peer_init      allocates the two buffers ([n_local sizes | cap_hashes hashes] each) and returns their IPC
+ *                  handles (2 x 64 bytes) for the caller to exchange (any transport; bench.py uses one all-gather);
+ *   peer_connect   handles of all ranks in rank order (world x 128 bytes) -> peer mappings;
+ *   sketch_publish after sketch_finish(_device): this rank's sketch -> its current buffer (asynchronous);
+ *   sketch_gather_peers   after a cross-rank barrier ON THE STREAM (e.g. a one-element all-reduce) so that every
+ *                  rank's publish has completed: concatenated CSR as kssd_b200_sketch_concat_device returns it.
+ * One barrier per step is enough: a buffer is rewritten two steps later, after a barrier its readers entered. */
+int kssd_b200_peer_init(kssd_ctx *ctx, uint32_t n_local, uint64_t cap_hashes, uint8_t *handles_out);
+int kssd_b200_peer_connect(kssd_ctx *ctx, const uint8_t *handles, uint32_t world, uint32_t rank);
+int kssd_b200_sketch_publish(kssd_ctx *ctx);
+int kssd_b200_sketch_gather_peers(kssd_ctx *ctx, const uint32_t **d_hashes, const uint64_t **d_genome_off,
+                                  uint64_t *total, int *overflow);
+
 /* ---- inverted index -----------------------------------------------------------------------------------
  * replaces transSketches, 32-bit path (src/sketch.cpp:970-1017): hash -> ascending genome ids.  The index is
  * kept in device memory as CSR over the DISTINCT hashes.  index_export gives the host the content of the

@@ -134,6 +134,27 @@ class Context:
                                                       C.byref(tot), C.byref(ov)))
         return ph.value or 0, po.value or 0, tot.value, bool(ov.value)
 
+    def peer_init(self, n_local, cap_hashes):
+        """Allocates this rank's two peer buffers -> their IPC handles (128 bytes)."""
+        buf = (C.c_uint8 * 128)()
+        check(self.lib.kssd_b200_peer_init(self.h, n_local, cap_hashes, buf))
+        return bytes(buf)
+
+    def peer_connect(self, handles, world, rank):
+        """handles: the 128-byte handle pairs of all ranks, rank order."""
+        assert len(handles) == 128 * world
+        buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
+        check(self.lib.kssd_b200_peer_connect(self.h, buf, world, rank))
+
+    def sketch_publish(self):
+        check(self.lib.kssd_b200_sketch_publish(self.h))
+
+    def sketch_gather_peers(self):
+        """-> (d_hashes, d_genome_off, total, overflow) over all ranks; call after a cross-rank barrier on the stream."""
+        ph, po, tot, ov = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_int()
+        check(self.lib.kssd_b200_sketch_gather_peers(self.h, C.byref(ph), C.byref(po), C.byref(tot), C.byref(ov)))
+        return ph.value or 0, po.value or 0, tot.value, bool(ov.value)
+
     def sketch(self, seq, genome_off, qual=None, least_qual=0, least_num_kmer=1, batch_bytes=None):
         """Sketch a packed batch (rabbitkssd_b200.synth.pack_batch layout) through pinned host batches.
         genome_off[n+1]: byte offsets; genome g owns [genome_off[g], genome_off[g+1]).  Large inputs are cut into

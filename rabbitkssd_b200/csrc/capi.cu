@@ -130,6 +130,7 @@ void kssd_b200_destroy(kssd_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    peer_release(c);
     DevBuf *dev[] = {&c->d_bitmap, &c->d_tab_keys, &c->d_emit, &c->d_cursor, &c->d_stage_seq[0], &c->d_stage_seq[1],
                      &c->d_stage_qual[0], &c->d_stage_qual[1], &c->d_stage_segoff[0], &c->d_stage_segoff[1], &c->d_stage_seggen[0],
                      &c->d_stage_seggen[1], &c->d_sort_tmp, &c->d_sort_counts, &c->d_keys_unique, &c->d_hashes, &c->d_genome_off,

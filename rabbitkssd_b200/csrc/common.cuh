@@ -75,6 +75,18 @@ struct kssd_batch_priv {
     kssd::HostBuf seq, qual, seg_off, seg_genome;
 };
 
+namespace kssd {
+static constexpr int kMaxPeers = 64;
+// multi-GPU gather over peer memory: two buffers per rank (double buffered), mapped into every rank with CUDA IPC
+struct PeerState {
+    uint32_t world = 0, rank = 0, n_local = 0;
+    uint64_t stride = 0;  // u32 words per block: n_local sizes + capacity in hashes
+    int flip = 0;
+    uint32_t *own[2] = {nullptr, nullptr};
+    uint32_t *peer[2][kMaxPeers] = {};
+};
+}  // namespace kssd
+
 struct kssd_ctx {
     int device = 0;
     int sm_count = 148;
@@ -110,6 +122,7 @@ struct kssd_ctx {
     int batch_next = 0;
     kssd::DevBuf d_sort_tmp, d_sort_counts, d_keys_unique;
     kssd::DevBuf d_hashes, d_genome_off;
+    kssd::PeerState peers;
     kssd::DevBuf d_cat_hashes, d_cat_off, d_cat_counts;  // sketch shards of all ranks, concatenated (multi-GPU gather epilogue)
     kssd::HostBuf h_hashes, h_genome_off, h_scalar;
     uint64_t sketch_total = 0;
@@ -148,6 +161,11 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
                        uint64_t *n_keep);   // segsort.cu: shared-memory per-genome sort + unique (fast path)
 int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total,
                   int *overflow);  // segsort.cu: multi-GPU gather epilogue
+int peer_init(kssd_ctx *c, uint32_t n_local, uint64_t cap_hashes, uint8_t *handles_out);
+int peer_connect(kssd_ctx *c, const uint8_t *handles, uint32_t world, uint32_t rank);
+void peer_release(kssd_ctx *c);
+int sketch_publish(kssd_ctx *c);
+int sketch_gather_peers(kssd_ctx *c, uint64_t *total, int *overflow);
 int genome_segments(kssd_ctx *c);           // segsort.cu: gcount -> seg_start + max count (no sync)
 int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_genomes, uint32_t *d_hashes,
                   uint64_t *d_genome_off);

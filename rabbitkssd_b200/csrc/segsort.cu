@@ -7,6 +7,8 @@
 // bitonic network as fallback), deduplicated / count-filtered there and written back.  HBM traffic: 8 B + 4 B per key
 // for the deal, 4 B + 4 B for the sort, 4 B + 4 B for the final packing -- against 6 radix passes x 48 B per key
 // for the device-wide sort it replaces (radix.cu, still used when a segment does not fit shared memory).
+#include <cstring>
+
 #include "common.cuh"
 
 namespace kssd {
@@ -289,33 +291,36 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
     return KSSD_OK;
 }
 
-// ---- multi-GPU gather epilogue: concatenate the all-gathered sketch shards ---------------------------------------
-// parts = world blocks of stride u32: [n_local sizes][hashes, genome-major][padding].  No host round trip between
-// the all-gather and the index build: sizes -> counts (one array), segment_scan_kernel -> offsets, one CTA per
-// genome copies its hashes.
-__global__ void __launch_bounds__(256) concat_counts_kernel(const uint32_t *__restrict__ parts, uint64_t stride, uint32_t n_local, uint32_t n_total,
-                                                            uint32_t *__restrict__ counts) {
+// ---- multi-GPU gather: concatenate the sketch shards of all ranks -----------------------------------------------
+// Block of rank r = [n_local sizes][hashes, genome-major][padding], `stride` u32 words.  The blocks are either the
+// pieces of one NCCL all-gather (contiguous in local memory) or -- the path bench.py uses -- the ranks' OWN
+// buffers read in place over NVLink through CUDA-IPC peer mappings (PartTable holds one pointer per rank): gather
+// and concatenation are then ONE pass of peer loads, no collective moves the data.  No host round trip either:
+// sizes -> counts (one array), segment_scan_kernel -> offsets, one CTA per genome copies its hashes.
+struct PartTable { const uint32_t *p[kMaxPeers]; };
+
+__global__ void __launch_bounds__(256) concat_counts_kernel(const PartTable parts, uint32_t n_local, uint32_t n_total, uint32_t *__restrict__ counts) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g < n_total) counts[g] = parts[(uint64_t)(g / n_local) * stride + g % n_local];
+    if (g < n_total) counts[g] = parts.p[g / n_local][g % n_local];
 }
 
-__global__ void __launch_bounds__(128) concat_copy_kernel(const uint32_t *__restrict__ parts, uint64_t stride, uint32_t n_local,
+__global__ void __launch_bounds__(128) concat_copy_kernel(const PartTable parts, uint64_t stride, uint32_t n_local,
                                                           const uint64_t *__restrict__ off, uint32_t *__restrict__ out,
                                                           unsigned long long *__restrict__ result /* [0] total, [1] overflow */) {
     const uint32_t g = blockIdx.x;
     const uint32_t r = g / n_local;
     const uint64_t r0 = off[(uint64_t)r * n_local], r1 = off[(uint64_t)(r + 1) * n_local];
-    if (r1 - r0 > stride - n_local) {  // the shard of rank r did not fit its block: every genome of it reports, nothing is copied
+    if (r1 - r0 > stride - n_local) {  // the shard of rank r did not fit its block: nothing of it is copied
         if (threadIdx.x == 0 && g % n_local == 0) atomicExch(result + 1, 1ull);
         return;
     }
     const uint64_t g0 = off[g], g1 = off[g + 1];
-    const uint32_t *src = parts + (uint64_t)r * stride + n_local + (g0 - r0);
+    const uint32_t *src = parts.p[r] + n_local + (g0 - r0);
     for (uint64_t i = threadIdx.x; i < g1 - g0; i += blockDim.x) out[g0 + i] = src[i];
     if (g == gridDim.x - 1 && threadIdx.x == 0) result[0] = g1;
 }
 
-int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow) {
+static int sketch_concat_table(kssd_ctx *c, const PartTable &parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow) {
     cudaStream_t st = c->stream;
     const uint32_t n_total = n_local * world;
     const uint64_t result_word = ((uint64_t)n_total + 1) & ~1ull;  // [counts n_total][pad][result: total, overflow (u64 each)]
@@ -324,9 +329,9 @@ int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_
     KSSD_TRY(c->d_cat_hashes.reserve(std::max<uint64_t>((stride - n_local) * world, 1) * 4, st));  // upper bound: every block full
     unsigned long long *result = reinterpret_cast<unsigned long long *>(c->d_cat_counts.as<uint32_t>() + result_word);
     KSSD_CUDA(cudaMemsetAsync(result, 0, 16, st));
-    concat_counts_kernel<<<(n_total + 255) / 256, 256, 0, st>>>(d_parts, stride, n_local, n_total, c->d_cat_counts.as<uint32_t>());
+    concat_counts_kernel<<<(n_total + 255) / 256, 256, 0, st>>>(parts, n_local, n_total, c->d_cat_counts.as<uint32_t>());
     segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_cat_counts.as<uint32_t>(), n_total, c->d_cat_off.as<uint64_t>(), nullptr);
-    concat_copy_kernel<<<n_total, 128, 0, st>>>(d_parts, stride, n_local, c->d_cat_off.as<uint64_t>(), c->d_cat_hashes.as<uint32_t>(), result);
+    concat_copy_kernel<<<n_total, 128, 0, st>>>(parts, stride, n_local, c->d_cat_off.as<uint64_t>(), c->d_cat_hashes.as<uint32_t>(), result);
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
     KSSD_TRY(c->h_scalar.reserve(64));
@@ -335,6 +340,86 @@ int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_
     *total = c->h_scalar.as<uint64_t>()[0];
     *overflow = c->h_scalar.as<uint64_t>()[1] != 0;
     return KSSD_OK;
+}
+
+int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow) {
+    if (world > kMaxPeers) { set_error("sketch_concat: at most %d ranks", kMaxPeers); return KSSD_E_ARG; }
+    PartTable t;
+    for (uint32_t r = 0; r < kMaxPeers; r++) t.p[r] = r < world ? d_parts + (uint64_t)r * stride : nullptr;
+    return sketch_concat_table(c, t, stride, n_local, world, total, overflow);
+}
+
+// ---- peer buffers: every rank publishes its shard in its own memory, the others read it over NVLink ---------------
+__global__ void __launch_bounds__(256) publish_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, uint32_t n_local,
+                                                      uint64_t n_copy, uint32_t *__restrict__ block) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_local + n_copy; i += (uint64_t)gridDim.x * blockDim.x)
+        block[i] = i < n_local ? (uint32_t)(genome_off[i + 1] - genome_off[i]) : hashes[i - n_local];
+}
+
+int peer_init(kssd_ctx *c, uint32_t n_local, uint64_t cap_hashes, uint8_t *handles_out) {
+    PeerState &ps = c->peers;
+    if (ps.own[0]) { set_error("peer_init: already initialised"); return KSSD_E_ARG; }
+    ps.n_local = n_local;
+    ps.stride = (uint64_t)n_local + cap_hashes;
+    for (int b = 0; b < 2; b++) {
+        KSSD_CUDA(cudaMalloc(&ps.own[b], ps.stride * 4 + 16));  // plain cudaMalloc: the whole allocation is what an IPC handle maps
+        cudaIpcMemHandle_t h;
+        KSSD_CUDA(cudaIpcGetMemHandle(&h, ps.own[b]));
+        static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+        memcpy(handles_out + 64 * b, &h, 64);
+    }
+    return KSSD_OK;
+}
+
+int peer_connect(kssd_ctx *c, const uint8_t *handles, uint32_t world, uint32_t rank) {
+    PeerState &ps = c->peers;
+    if (!ps.own[0] || world == 0 || world > kMaxPeers || rank >= world) { set_error("peer_connect: peer_init first; 1..%d ranks", kMaxPeers); return KSSD_E_ARG; }
+    for (uint32_t r = 0; r < world; r++)
+        for (int b = 0; b < 2; b++) {
+            if (r == rank) { ps.peer[b][r] = ps.own[b]; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, handles + ((size_t)r * 2 + b) * 64, 64);
+            void *p = nullptr;
+            KSSD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+            ps.peer[b][r] = static_cast<uint32_t *>(p);
+        }
+    ps.world = world;
+    ps.rank = rank;
+    return KSSD_OK;
+}
+
+void peer_release(kssd_ctx *c) {
+    PeerState &ps = c->peers;
+    for (uint32_t r = 0; r < ps.world; r++)
+        for (int b = 0; b < 2; b++)
+            if (r != ps.rank && ps.peer[b][r]) cudaIpcCloseMemHandle(ps.peer[b][r]);
+    for (int b = 0; b < 2; b++)
+        if (ps.own[b]) cudaFree(ps.own[b]);
+    ps = PeerState();
+}
+
+// the ctx's finished sketch (d_hashes, d_genome_off of sketch_finish) -> its own peer buffer; stream-ordered, no sync
+int sketch_publish(kssd_ctx *c) {
+    PeerState &ps = c->peers;
+    if (!ps.world) { set_error("sketch_publish: peer_connect first"); return KSSD_E_ARG; }
+    if (c->n_genomes != ps.n_local) { set_error("sketch_publish: %u genomes in the session, peer buffers hold %u", c->n_genomes, ps.n_local); return KSSD_E_ARG; }
+    ps.flip ^= 1;  // double buffer: the peers may still be reading the previous step's block
+    const uint64_t n_copy = std::min<uint64_t>(c->sketch_total, ps.stride - ps.n_local);  // a larger shard shows as overflow at the readers
+    const uint64_t n = ps.n_local + n_copy;
+    publish_kernel<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 8), 256, 0, c->stream>>>(c->d_hashes.as<uint32_t>(), c->d_genome_off.as<uint64_t>(),
+                                                                                                ps.n_local, n_copy, ps.own[ps.flip]);
+    KSSD_CUDA(cudaGetLastError());
+    c->launches++;
+    return KSSD_OK;
+}
+
+// after a cross-rank barrier on the stream (every rank's publish has completed): pull + concatenate all shards
+int sketch_gather_peers(kssd_ctx *c, uint64_t *total, int *overflow) {
+    PeerState &ps = c->peers;
+    if (!ps.world) { set_error("sketch_gather_peers: peer_connect first"); return KSSD_E_ARG; }
+    PartTable t;
+    for (uint32_t r = 0; r < kMaxPeers; r++) t.p[r] = r < ps.world ? ps.peer[ps.flip][r] : nullptr;
+    return sketch_concat_table(c, t, ps.stride, ps.n_local, ps.world, total, overflow);
 }
 
 }  // namespace kssd

@@ -57,6 +57,32 @@ def rect_bounds(n_query, parts):
     return b
 
 
+class PeerGather:
+    """Sketch gather over peer memory (NVLink through CUDA IPC) instead of an NCCL transfer: every rank publishes its
+    shard in its own buffer and reads the others' in place while concatenating (kssd_b200_sketch_gather_peers).
+    torch.distributed only carries the 128-byte IPC handles once and a one-element all-reduce per step as the barrier."""
+
+    def __init__(self, dist, ctx, n_local, cap, rank, world):
+        self.dist, self.ctx, self.world = dist, ctx, world
+        dev = torch.device("cuda", torch.cuda.current_device())
+        mine = torch.frombuffer(bytearray(ctx.peer_init(n_local, cap)), dtype=torch.uint8).to(dev)
+        every = torch.empty(128 * world, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(every, mine)
+        ctx.peer_connect(bytes(every.cpu().numpy().tobytes()), world, rank)
+        self.token = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def gather(self):
+        """After ctx.sketch_finish_device(): -> (d_hashes ptr, d_genome_off ptr, total) or None on overflow (every rank alike)."""
+        t0 = _tick("", time.perf_counter()) if TRACE is not None else 0.0
+        self.ctx.sketch_publish()
+        t0 = _tick("peer.publish", t0)
+        self.dist.all_reduce(self.token)  # barrier on the stream: every rank's publish precedes its contribution
+        t0 = _tick("peer.barrier", t0)
+        ph, po, total, overflow = self.ctx.sketch_gather_peers()
+        _tick("peer.pull", t0)
+        return None if overflow else (ph, po, total)
+
+
 def gather_sketches_device(dist, ctx, hashes_local, sizes_local, world, cap):
     """CUDA fast path of gather_sketches: ONE all-gather of equally sized blocks [n_local sizes | hashes | padding to
     cap] and the library's concat kernels (kssd_b200_sketch_concat_device) -- no host round trip for the shard sizes,

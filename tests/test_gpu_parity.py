@@ -304,3 +304,41 @@ def test_index_sharded_by_hash_range_equals_full_build(parts):
         assert ov and c.index_adopt_parts(small.data_ptr(), 16, 1, d_o.data_ptr(), n)
     finally:
         c.close()
+
+
+def test_peer_gather_single_rank():
+    """Peer-memory gather with world = 1 (the own buffer stands in for the peers; the IPC mappings themselves need
+    two processes and are exercised by bench.py --gpus N): publish + pull returns the session's sketch, twice
+    (double buffer flip), and a shard larger than the buffer reports overflow."""
+    import torch
+    k, s, l = 10, 6, 3
+    fams = synth.family(31, 6, 150000, 0.03, n_contigs=2)
+    c = api.Context(0)
+    try:
+        c.set_params(k, s, l, util.shuffled_dim(k, s, l))
+        seq, _, off = synth.pack_batch(fams)
+        c.peer_connect(c.peer_init(len(fams), 4096), 1, 0)
+
+        class View:
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+        for _ in range(3):
+            h, goff = c.sketch(seq, off)
+            h, goff = np.array(h, copy=True), np.array(goff, copy=True)
+            c.sketch_publish()
+            ph, po, total, overflow = c.sketch_gather_peers()
+            assert not overflow and total == len(h)
+            got_h = torch.as_tensor(View(ph, total, "<i4"), device="cuda").cpu().numpy().view(np.uint32)
+            got_o = torch.as_tensor(View(po, len(fams) + 1, "<i8"), device="cuda").cpu().numpy()
+            assert np.array_equal(got_h, h) and np.array_equal(got_o.astype(np.uint64), goff.astype(np.uint64))
+    finally:
+        c.close()
+    c = api.Context(0)
+    try:
+        c.set_params(k, s, l, util.shuffled_dim(k, s, l))
+        c.peer_connect(c.peer_init(len(fams), 16), 1, 0)  # far too small
+        c.sketch(seq, off)
+        c.sketch_publish()
+        assert c.sketch_gather_peers()[3]
+    finally:
+        c.close()
