@@ -241,7 +241,6 @@ def run_b200(args):
     import torch.distributed as dist
     from rabbitkssd_b200 import api
     from rabbitkssd_b200.multigpu import PeerGather, build_index_sharded, gather_sketches, gather_sketches_device, triangle_bounds
-    import oracle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -262,7 +261,7 @@ def run_b200(args):
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     ctx.set_stream(stream.cuda_stream)
-    dim = oracle.shuffle_dim(K, S, L_)  # the .shuf table is an INPUT of the path (glibc-rand permutation)
+    dim = api.shuffle_table(K, S, L_)  # the .shuf table is an INPUT of the path (glibc-rand permutation, host code)
     ctx.set_params(K, S, L_, dim)
     ctx.set_profiling(True)
 

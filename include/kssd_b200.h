@@ -35,6 +35,11 @@ typedef struct kssd_ctx kssd_ctx;
 const char *kssd_b200_last_error(void);
 int kssd_b200_version(void);
 
+/* Host only, no device needed: the dimension-reduction table `rabbit_kssd shuffle -k -s -l` writes into a .shuf file
+ * (src/shuffle.cpp:48-54, :76-104; glibc srand/rand Fisher-Yates).  out: 16^half_subk ints.  The table is an input of
+ * the GPU path (kssd_b200_set_params); generating it stays on the CPU as in the reference. */
+int kssd_b200_shuffle_table(int half_k, int half_subk, int drlevel, int32_t *out);
+
 /* Create a context on CUDA device `device`.  Fails (KSSD_E_CUDA) when no device is usable. */
 int kssd_b200_init(kssd_ctx **ctx, int device);
 void kssd_b200_destroy(kssd_ctx *ctx);

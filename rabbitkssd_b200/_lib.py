@@ -29,6 +29,7 @@ SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(Hit), C.c_size_t)
 SYMBOLS = {
     "kssd_b200_last_error": (C.c_char_p, []),
     "kssd_b200_version": (C.c_int, []),
+    "kssd_b200_shuffle_table": (C.c_int, [C.c_int, C.c_int, C.c_int, i32p]),
     "kssd_b200_init": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "kssd_b200_destroy": (None, [C.c_void_p]),
     "kssd_b200_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -16,6 +16,13 @@ def _np_from_ptr(ptr, n, dtype):
     return np.frombuffer(buf, dtype=dtype, count=n).copy()
 
 
+def shuffle_table(half_k, half_subk, drlevel):
+    """The .shuf dimension-reduction table (host code of the library, src/shuffle.cpp:76-104): int32[16^half_subk]."""
+    out = np.empty(1 << (4 * half_subk), dtype=np.int32)
+    check(_lib.load().kssd_b200_shuffle_table(half_k, half_subk, drlevel, out.ctypes.data_as(_lib.i32p)))
+    return out
+
+
 class Context:
     def __init__(self, device=0):
         self.lib = _lib.load()

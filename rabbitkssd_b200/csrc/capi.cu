@@ -1,6 +1,7 @@
 // extern "C" entry points of libkssd_b200.so (declared in include/kssd_b200.h) + small runtime helpers.
 #include <algorithm>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -97,6 +98,25 @@ extern "C" {
 
 const char *kssd_b200_last_error(void) { return g_err; }
 int kssd_b200_version(void) { return 100; }
+
+// Host only: the shuffle table is an INPUT of the GPU path and its generation stays on the CPU, as in the reference
+// (src/shuffle.cpp:76-104 shuffleN/shuffle, :48-54 write_shuffle_dim_file): identity permutation of 16^half_subk ints,
+// Fisher-Yates with glibc srand(23), then again with srand(id), id = (half_k << 8) + (half_subk << 4) + drlevel,
+// j = rand() % (i + 1).  Same glibc => the same table as `rabbit_kssd shuffle` writes.
+int kssd_b200_shuffle_table(int half_k, int half_subk, int drlevel, int32_t *out) {
+    if (!out || half_subk < 1 || half_subk > 7 || half_k < half_subk || drlevel < 0 || drlevel >= half_subk) {
+        set_error("shuffle_table: need 1 <= half_subk <= 7, half_k >= half_subk, 0 <= drlevel < half_subk");
+        return KSSD_E_ARG;
+    }
+    const int n = 1 << (4 * half_subk);
+    for (int i = 0; i < n; i++) out[i] = i;
+    const unsigned seeds[2] = {23u, (unsigned)((half_k << 8) + (half_subk << 4) + drlevel)};
+    for (unsigned seed : seeds) {
+        srand(seed);
+        for (int i = n - 1; i > 0; i--) std::swap(out[i], out[rand() % (i + 1)]);
+    }
+    return KSSD_OK;
+}
 
 int kssd_b200_init(kssd_ctx **out, int device) {
     if (!out) { set_error("null out pointer"); return KSSD_E_ARG; }

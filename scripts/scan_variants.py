@@ -22,7 +22,6 @@ def main():
     import numpy as np
     import torch
     import bench
-    import oracle
     from rabbitkssd_b200 import api
     length, family = 5_000_000, 10
     stride = (length + 2 + 15) // 16 * 16  # as bench.py
@@ -30,7 +29,7 @@ def main():
     buf = bench.gen_genomes_device(torch, n, 0, length, family, stride)
     d_seg_off = torch.from_numpy((np.arange(n + 1, dtype=np.int64) * stride)).cuda()
     d_seg_gen = torch.arange(n, dtype=torch.int32, device="cuda")
-    dim = oracle.shuffle_dim(bench.K, bench.S, bench.L_)
+    dim = api.shuffle_table(bench.K, bench.S, bench.L_)
     ref_tot = None
     for v in [args.tag]:
         ctx = api.Context(0)

@@ -36,3 +36,25 @@ def test_init_fails_loudly_without_gpu():
     with pytest.raises(_lib.KssdError) as e:
         api.Context(0)
     assert "no CPU fallback" in str(e.value)
+
+
+def test_shuffle_table_equals_reference_shuf_file():
+    """Host-only entry point (no GPU needed): kssd_b200_shuffle_table == the table inside the .shuf file the unmodified
+    reference binary wrote when the golden fixtures were made (SHA-256 pinned in tests/golden/golden.json)."""
+    import numpy as np
+    import util
+    from rabbitkssd_b200 import _lib, api
+    seen = set()
+    for case, m in util.golden_meta().items():
+        c = m["recipe"]
+        key = (c["k"], c["s"], c["l"])
+        if key in seen or c["s"] > 6:  # the s = 7 table is 1 GiB: covered through the oracle's copy in the GPU tests
+            continue
+        seen.add(key)
+        dim = api.shuffle_table(*key)
+        assert util.shuf_sha256(*key, dim) == m["shuf_sha256"], case
+    assert len(seen) >= 3
+    with pytest.raises(_lib.KssdError):
+        api.shuffle_table(10, 8, 3)
+    with pytest.raises(_lib.KssdError):
+        np.asarray(api.shuffle_table(4, 6, 3))
