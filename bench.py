@@ -273,9 +273,9 @@ def run_b200(args):
     n_bytes = n_local * stride
     sk_size = length / 16.0 ** L_                      # expected hashes per genome
     gather_cap = int(1.25 * n_local * sk_size) + 1024  # block size of the sketch all-gather, the same on every rank
-    # rows cost their cells plus the posting-range lookups of their hashes (measured at N=1: list_lookup_kernel
-    # 0.031 us per hash, dist_tile_kernel 5.9e-6 us per cell -> ~5 cell-equivalents per hash)
-    bounds = triangle_bounds(n_total, world, row_cost=5.0 * sk_size)
+    # a row costs its cells plus per-hash work (posting-range lookup, posting streaming).  Fitted to the dist phase of
+    # the 1- and 8-GPU runs (profiles/r01x): ~50 cell-equivalents per hash, i.e. the per-row part dominates
+    bounds = triangle_bounds(n_total, world, row_cost=40.0 * sk_size)
     r0, r1 = bounds[rank], bounds[rank + 1]
     state = {}
     if world > 1 and not args.nccl_gather:

@@ -123,6 +123,8 @@ struct kssd_ctx {
     kssd::DevBuf d_sort_tmp, d_sort_counts, d_keys_unique;
     kssd::DevBuf d_hashes, d_genome_off;
     kssd::PeerState peers;
+    uint64_t cat_total = 0;  // hashes in d_cat_hashes (valid while cat_n != 0)
+    uint32_t cat_n = 0;      // genomes in d_cat_off
     kssd::DevBuf d_cat_hashes, d_cat_off, d_cat_counts;  // sketch shards of all ranks, concatenated (multi-GPU gather epilogue)
     kssd::HostBuf h_hashes, h_genome_off, h_scalar;
     uint64_t sketch_total = 0;

@@ -339,6 +339,8 @@ static int sketch_concat_table(kssd_ctx *c, const PartTable &parts, uint64_t str
     KSSD_CUDA(cudaStreamSynchronize(st));
     *total = c->h_scalar.as<uint64_t>()[0];
     *overflow = c->h_scalar.as<uint64_t>()[1] != 0;
+    c->cat_total = *total;
+    c->cat_n = *overflow ? 0 : n_total;
     return KSSD_OK;
 }
 
