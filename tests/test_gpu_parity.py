@@ -342,3 +342,43 @@ def test_peer_gather_single_rank():
         assert c.sketch_gather_peers()[3]
     finally:
         c.close()
+
+
+def _retained_repeat_unit(k, s, l, seed=5):
+    """A 2k-base unit whose tandem repeat emits (one of its rotations is a retained k-mer)."""
+    for t in range(5000):
+        unit = synth.random_bases(seed * 100003 + t, 2 * k)
+        if len(util.oracle_sketch(k, s, l, [[np.tile(unit, 4)]])[0]):
+            return unit
+    raise AssertionError("no retained repeat unit found")
+
+
+def test_tandem_repeats_duplicates_and_overflow_report(ctx):
+    """Repeat-rich input: a tandem repeat of a retained k-mer emits the same hash once per period -- thousands of
+    duplicates that the per-genome sort + unique must collapse exactly like the reference's unordered_set
+    (src/sketch.cpp:526-529).  Far beyond the emit buffer's headroom the library reports KSSD_E_OVERFLOW instead of
+    returning a truncated sketch."""
+    from rabbitkssd_b200 import _lib
+    k, s, l = 10, 6, 3
+    unit = _retained_repeat_unit(k, s, l)
+    base = synth.random_bases(911, 400000)
+    genomes = [
+        [np.concatenate([base[:150000], np.tile(unit, 20000), base[150000:]])],       # 400 kbp of repeat: ~20 k duplicate emits
+        [np.tile(unit, 3000), base[:50000], np.tile(unit[::-1].copy(), 3000)],        # repeats at record borders
+        [base],
+    ]
+    want = util.oracle_sketch(k, s, l, genomes)
+    got, _, _ = _gpu_sketch(ctx, k, s, l, genomes)
+    for g, (a, b) in enumerate(zip(got, want)):
+        assert np.array_equal(a.astype(np.uint64), b), g
+    # 120 Mbp of pure repeat: one emit per period = 6 M emits against a capacity of 8 x 120e6 / 4096 + 4 Mi = 4.4 M:
+    # must fail loudly
+    huge = [[np.tile(unit, 6_000_000)]]
+    ctx.set_params(k, s, l, util.shuffled_dim(k, s, l))
+    seq, _, off = synth.pack_batch(huge)
+    with pytest.raises(_lib.KssdError) as e:
+        ctx.sketch(seq, off)
+    assert e.value.code == -5 and "overflow" in str(e.value)
+    # the context stays usable
+    got, _, _ = _gpu_sketch(ctx, k, s, l, genomes[2:])
+    assert np.array_equal(got[0].astype(np.uint64), want[2])
