@@ -371,9 +371,9 @@ def test_tandem_repeats_duplicates_and_overflow_report(ctx):
     got, _, _ = _gpu_sketch(ctx, k, s, l, genomes)
     for g, (a, b) in enumerate(zip(got, want)):
         assert np.array_equal(a.astype(np.uint64), b), g
-    # 120 Mbp of pure repeat: one emit per period = 6 M emits against a capacity of 8 x 120e6 / 4096 + 4 Mi = 4.4 M:
-    # must fail loudly
-    huge = [[np.tile(unit, 6_000_000)]]
+    # 400 Mbp of pure repeat: one emit per period = 20 M emits against a capacity of 8 x 400e6 / 4096 + 4 Mi = 5 M
+    # (the allocator may round that up, hence the margin): must fail loudly
+    huge = [[np.tile(unit, 20_000_000)]]
     ctx.set_params(k, s, l, util.shuffled_dim(k, s, l))
     seq, _, off = synth.pack_batch(huge)
     with pytest.raises(_lib.KssdError) as e:
