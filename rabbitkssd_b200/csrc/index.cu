@@ -129,7 +129,16 @@ int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
 // 4 radix passes x 48 B of the device-wide sort below (kept for bucket overflow, i.e. heavily skewed hashes).
 static constexpr uint32_t kBucketCapSmall = 3072, kBucketCapLarge = 8192;  // pairs per bucket: 24 KB / 64 KB of shared memory; the hash density falls
                                                                            // linearly (see range_begin), so the first buckets hold 2 x the mean of ~750-1000
-static constexpr uint32_t kSubBuckets = 1024;                               // counting-sort buckets inside a bucket
+#ifndef KSSD_SUB_BUCKETS
+#define KSSD_SUB_BUCKETS 512  // measured: 512 and 256 are 7 % faster than 1024 for the index build (profiles/r01y_index_variants.txt)
+#endif
+#ifndef KSSD_SORT_THREADS
+#define KSSD_SORT_THREADS 256
+#endif
+#ifndef KSSD_BUCKET_LOG
+#define KSSD_BUCKET_LOG 10
+#endif
+static constexpr uint32_t kSubBuckets = KSSD_SUB_BUCKETS;                               // counting-sort buckets inside a bucket
 
 // Both passes can be restricted to the hashes in [h_lo, h_last] (multi-GPU: every rank builds the CSR of one hash range,
 // index_build_range); buckets are then relative to h_lo.
@@ -158,12 +167,12 @@ __global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__rest
 
 // One CTA per bucket.  Writes the postings of the bucket (dict), its distinct hashes + list starts (compacted at the
 // head of the bucket's range of tmp_hash / tmp_rel), their number, and folds the largest hash into *max_hash.
-__global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart, int shift,
+__global__ void __launch_bounds__(KSSD_SORT_THREADS) bucket_sort_kernel(const uint64_t *__restrict__ pairs, const uint64_t *__restrict__ bstart, int shift,
                                                           uint32_t h_lo, uint32_t cap, uint32_t *__restrict__ dict, uint32_t *__restrict__ tmp_hash,
                                                           uint32_t *__restrict__ tmp_rel, uint32_t *__restrict__ hcount,
                                                           uint32_t *__restrict__ flags /* [0] overflow, [1] max hash */) {
     extern __shared__ uint64_t s_pairs[];
-    __shared__ uint32_t warp_sums[8];
+    __shared__ uint32_t warp_sums[KSSD_SORT_THREADS / 32];
     __shared__ uint32_t running;
     const uint32_t b = blockIdx.x;
     const uint64_t b0 = bstart[b];
@@ -178,7 +187,8 @@ __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__rest
     const uint32_t n = (uint32_t)n64;
     if (threadIdx.x == 0) running = 0;
     {   // sub-bucket = the hash bits below the bucket prefix (clamped: the last bucket also holds out-of-range hashes)
-        const int sub_shift = shift > 10 ? shift - 10 : 0;
+        constexpr int kSubLog = KSSD_SUB_BUCKETS == 2048 ? 11 : KSSD_SUB_BUCKETS == 1024 ? 10 : KSSD_SUB_BUCKETS == 512 ? 9 : 8;
+        const int sub_shift = shift > kSubLog ? shift - kSubLog : 0;
         const uint32_t first = (uint32_t)(((uint64_t)b << shift) >> sub_shift);
         count_sort_smem<uint64_t>(pairs + b0, s_pairs, reinterpret_cast<uint32_t *>(s_pairs + cap), n, kSubBuckets,
                                   [=](uint64_t k) { return min((((uint32_t)(k >> 32) - h_lo) >> sub_shift) - first, kSubBuckets - 1); });
@@ -197,7 +207,7 @@ __global__ void __launch_bounds__(256) bucket_sort_kernel(const uint64_t *__rest
         if (lane == 0) warp_sums[w] = __popc(bal);
         __syncthreads();
         uint32_t wp = 0, tot = 0;
-        for (int q = 0; q < 8; q++) { const uint32_t x = warp_sums[q]; if (q < w) wp += x; tot += x; }
+        for (int q = 0; q < KSSD_SORT_THREADS / 32; q++) { const uint32_t x = warp_sums[q]; if (q < w) wp += x; tot += x; }
         if (head) {
             const uint64_t at = b0 + running + wp + __popc(bal & ((1u << lane) - 1));
             tmp_hash[at] = (uint32_t)(v >> 32);
@@ -238,7 +248,7 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     cudaStream_t st = c->stream;
     *done = false;
     int B = 0;
-    while (B < 18 && (expect >> (B + 10)) > 0) B++;  // ~1 k pairs per bucket on average
+    while (B < 18 && (expect >> (B + KSSD_BUCKET_LOG)) > 0) B++;  // ~1 k pairs per bucket on average
     if (B > range_bits) B = range_bits;
     const int shift = range_bits - B;
     const uint32_t nb = 1u << B;
@@ -271,7 +281,7 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     // small shared-memory footprint first (more CTAs per SM); one retry with the large one when a bucket overflowed
     for (uint32_t cap : {kBucketCapSmall, kBucketCapLarge}) {
         KSSD_CUDA(cudaMemsetAsync(flags, 0, 16, st));
-        bucket_sort_kernel<<<nb, 256, (size_t)cap * 8 + kSubBuckets * 4, st>>>(c->d_pairs.as<uint64_t>(), bstart, shift, h_lo, cap, c->d_dict.as<uint32_t>(),
+        bucket_sort_kernel<<<nb, KSSD_SORT_THREADS, (size_t)cap * 8 + kSubBuckets * 4, st>>>(c->d_pairs.as<uint64_t>(), bstart, shift, h_lo, cap, c->d_dict.as<uint32_t>(),
                                                                                tmp_hash, tmp_rel, hcount, flags);
         segment_scan_kernel<<<1, 1024, 0, st>>>(hcount, nb, hstart, nullptr);
         bucket_pack_kernel<<<nb, 128, 0, st>>>(bstart, hstart, tmp_hash, tmp_rel, nb, c->d_uniq_hash.as<uint32_t>(), c->d_uniq_off.as<uint64_t>());
