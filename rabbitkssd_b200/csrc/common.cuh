@@ -95,6 +95,7 @@ struct kssd_ctx {
     cudaStream_t copy_stream = nullptr;
     uint64_t launches = 0;
     bool profiling = false;
+    uint64_t attr_mask = 0;    // kernels whose dynamic shared-memory limit was raised ON THIS DEVICE (cudaFuncSetAttribute is per device)
     bool force_radix = false;  // tests: take the device-wide radix paths even when the shared-memory fast paths apply
 
     // parameters + tables

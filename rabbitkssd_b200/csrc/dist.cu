@@ -331,11 +331,11 @@ int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_
     a.hit_cursor = d_cursor;
     a.list_word_off = (uint32_t)(cnt_smem / 4);
 
-    static bool attr_done = false;
-    if (!attr_done) {
+    const uint64_t attr_bit = 1ull << (42);
+    if (!(c->attr_mask & attr_bit)) {
         KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
         KSSD_CUDA(cudaFuncSetAttribute(dist_tile_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
-        attr_done = true;
+        c->attr_mask |= attr_bit;
     }
     uint64_t hit_cap = c->d_hits.cap / sizeof(kssd_hit);
     if (hit_cap == 0) {

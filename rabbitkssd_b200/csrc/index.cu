@@ -270,10 +270,10 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
                                                                 c->d_pairs.as<uint64_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
-    static bool attr_done = false;
-    if (!attr_done) {
+    const uint64_t attr_bit = 1ull << (40);
+    if (!(c->attr_mask & attr_bit)) {
         KSSD_CUDA(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBucketCapLarge * 8 + kSubBuckets * 4)));
-        attr_done = true;
+        c->attr_mask |= attr_bit;
     }
     KSSD_TRY(c->h_scalar.reserve(64));
     uint64_t *hs = c->h_scalar.as<uint64_t>();

@@ -259,10 +259,10 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
         genome_deal_kernel<<<(unsigned)((n_emit + 255) / 256), 256, 0, st>>>(d_emit, c->d_emit_rank.as<uint32_t>(), n_emit, ng, seg_start, seg);
         c->launches++;
     }
-    static bool attr_done = false;
-    if (!attr_done) {
+    const uint64_t attr_bit = 1ull << (41);
+    if (!(c->attr_mask & attr_bit)) {
         KSSD_CUDA(cudaFuncSetAttribute(genome_sort_unique_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSegSortMaxKeys * 4)));
-        attr_done = true;
+        c->attr_mask |= attr_bit;
     }
     const int threads = max_count <= 2048 ? 256 : max_count <= 8192 ? 512 : 1024;
     const uint32_t key_cap = std::max<uint32_t>(max_count, 1);

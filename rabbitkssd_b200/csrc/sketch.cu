@@ -541,10 +541,10 @@ int build_tables(kssd_ctx *c, const int32_t *shuffled_dim) {
 
 template <int G, int W0, bool A32>
 static int launch_one(kssd_ctx *c, const ScanArgs &a, size_t smem) {
-    static bool attr_done = false;  // one flag per template instantiation
-    if (!attr_done) {
+    const uint64_t attr_bit = 1ull << (G * 4 + W0 * 2 + (A32 ? 1 : 0));
+    if (!(c->attr_mask & attr_bit)) {
         KSSD_CUDA(cudaFuncSetAttribute(kssd_scan_kernel<G, W0, A32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
-        attr_done = true;
+        c->attr_mask |= attr_bit;
     }
     uint64_t ctas = std::min<uint64_t>(((uint64_t)a.n_tiles + kScanWarps - 1) / kScanWarps, (uint64_t)c->sm_count);
     if (ctas == 0) return KSSD_OK;
