@@ -69,6 +69,20 @@ def read_index_dict(index_path, dict_path):
     return counts, postings
 
 
+def read_index_dict64(index_path, dict_path):
+    """64-bit hash variant (half_k - drlevel > 8, src/sketch.cpp:904-969): .index = size_t n; u64 hash[n]; u32 count[n]
+    in the iteration order of the reference's hash map, .dict = the posting lists in the same order.
+    Returns (hashes u64[n], counts u32[n], postings u32[sum counts])."""
+    with open(index_path, "rb") as f:
+        (n,) = struct.unpack("<Q", f.read(8))
+        hashes = np.fromfile(f, dtype=np.uint64, count=n)
+        counts = np.fromfile(f, dtype=np.uint32, count=n)
+    postings = np.fromfile(dict_path, dtype=np.uint32)
+    if len(hashes) != n or len(counts) != n or int(counts.sum()) != len(postings):
+        raise IOError("read_index_dict64: mismatched sizes")
+    return hashes, counts, postings
+
+
 def parse_dist_text(path):
     """Parse .alldist/.dist text into a set of canonical tuples
     (name_a, name_b, common, size0, size1, jorc_text, dist_text); header lines are skipped."""

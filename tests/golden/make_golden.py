@@ -5,6 +5,7 @@
 The reference ships no golden vectors; these files pin parity to the reference's own
 CPU output.  Inputs are NOT stored: they are regenerated from the seeds in cases() by rabbitkssd_b200.synth
 (counter-based splitmix64, machine independent).  Run from the repo root:  python tests/golden/make_golden.py
+[case ...] (no names = all cases).
 """
 import hashlib
 import json
@@ -34,6 +35,10 @@ def cases():
                           contigs=3, max_div=0.05, n_runs=4, lower=0.05, D=0.3, N=3),
         "fa_k10s7l4": dict(kind="fasta", k=10, s=7, l=4, seed=20261107, n_fam=1, fam=3, length=1500000,
                            contigs=2, max_div=0.02, n_runs=5, lower=0.01, D=0.3, N=1),
+        # half_k - drlevel = 9 > 8: the reference's 64-bit hash path (36-bit hashes, sparse .index).
+        # Pins the ORACLE for the next round; the CUDA library refuses this configuration (KSSD_E_UNSUPPORTED).
+        "fa_k12s6l3": dict(kind="fasta", k=12, s=6, l=3, seed=20261109, n_fam=2, fam=3, length=250000,
+                           contigs=2, max_div=0.03, n_runs=4, lower=0.02, D=0.3, N=2),
         "fq_k10s6l3": dict(kind="fastq", k=10, s=6, l=3, seed=20261108, n_fam=2, fam=2, length=120000,
                            read_len=150, coverage=3, Q=40, n=2, D=0.5, N=1),
     }
@@ -104,7 +109,12 @@ def main():
     if not os.access(REF, os.X_OK):
         sys.exit("reference binary missing: run oracle/build_ref.sh first")
     meta = {}
+    only = sys.argv[1:]  # optional: names of the cases to (re)generate; the others are kept as they are in golden.json
+    if only and os.path.exists(os.path.join(HERE, "golden.json")):
+        meta = json.load(open(os.path.join(HERE, "golden.json")))
     for cname, c in cases().items():
+        if only and cname not in only:
+            continue
         with tempfile.TemporaryDirectory() as d:
             names = write_inputs(c, d)
             shuf = "x.shuf"
@@ -116,8 +126,16 @@ def main():
             run([REF, "sketch", "-L", shuf, "-i", "list.txt", "-o", "ref", "-t", "4"] + extra, d)
             info, snames, sets = formats.read_sketch(os.path.join(d, "ref.sketch"))
             by_name = {n: np.sort(s.astype(np.uint64)) for n, s in zip(snames, sets)}
-            counts, postings = formats.read_index_dict(os.path.join(d, "ref.sketch.index"),
-                                                       os.path.join(d, "ref.sketch.dict"))
+            use64 = c["k"] - c["l"] > 8
+            if use64:  # sparse index in hash-map iteration order: stored as the file has it
+                ihash, icount, postings = formats.read_index_dict64(os.path.join(d, "ref.sketch.index"),
+                                                                    os.path.join(d, "ref.sketch.dict"))
+                # posting ids follow the order of ref.sketch (completion order): remap to list order
+                file_to_list = np.array([names.index(n) for n in snames], dtype=np.uint32)
+                postings = file_to_list[postings]
+            else:
+                counts, postings = formats.read_index_dict(os.path.join(d, "ref.sketch.index"),
+                                                           os.path.join(d, "ref.sketch.dict"))
             # canonical sketch file in list order so that alldist/dist orientation is reproducible
             hashes = np.concatenate([by_name[n] for n in names])
             off = np.concatenate([[0], np.cumsum([len(by_name[n]) for n in names])]).astype(np.uint64)
@@ -133,11 +151,15 @@ def main():
             }.items():
                 run([REF] + args + ["-t", "3"], d)
                 out[tag] = sorted(formats.parse_dist_text(os.path.join(d, args[-1])))
-            nz = np.nonzero(counts)[0]
+            if use64:
+                index_hash, index_count, hash_size = ihash, icount, int(len(ihash))
+            else:
+                nz = np.nonzero(counts)[0]
+                index_hash, index_count, hash_size = nz.astype(np.uint64), counts[nz], int(len(counts))
             np.savez_compressed(os.path.join(HERE, cname + ".npz"),
                                 **{"set_" + n: by_name[n] for n in names},
-                                index_hash=nz.astype(np.uint64), index_count=counts[nz], dict=postings)
-            meta[cname] = dict(recipe=c, shuf_sha256=sha, names=names, info=info, hash_size=int(len(counts)),
+                                index_hash=index_hash, index_count=index_count, dict=postings)
+            meta[cname] = dict(recipe=c, shuf_sha256=sha, names=names, info=info, hash_size=hash_size,
                                lines=out)
             print(cname, "ok:", {n: len(by_name[n]) for n in names}, {k: len(v) for k, v in out.items()})
     with open(os.path.join(HERE, "golden.json"), "w") as f:
