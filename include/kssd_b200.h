@@ -28,7 +28,7 @@ extern "C" {
 #define KSSD_E_ARG (-2)         /* bad argument / call order */
 #define KSSD_E_UNSUPPORTED (-3) /* configuration the library does not implement (64-bit hashes) */
 #define KSSD_E_PARAM (-4)       /* half_subk - drlevel < 3: the reference aborts here (common.cpp:37-39) */
-#define KSSD_E_OVERFLOW (-5)    /* an output buffer was too small; text says which and the size needed */
+#define KSSD_E_OVERFLOW (-5)    /* an output buffer stayed too small after regrowing; text says which and the size needed */
 
 typedef struct kssd_ctx kssd_ctx;
 
@@ -86,7 +86,10 @@ int kssd_b200_batch_acquire(kssd_ctx *ctx, kssd_batch **batch, uint64_t min_capa
 /* Async H2D + scan kernel; the batch may be re-acquired once the copy has drained. */
 int kssd_b200_batch_submit(kssd_ctx *ctx, kssd_batch *batch);
 /* Same scan on a buffer ALREADY resident in device memory (bench `value`, multi-GPU pipelines). d_seq must be
- * 16-byte aligned; d_seg_off/d_seg_genome are device arrays. */
+ * 16-byte aligned; d_seg_off/d_seg_genome are device arrays.  All buffers passed to sketch_scan_device / _scan_host must
+ * stay valid and unchanged until sketch_finish returns: when a repeat-rich input emits more keys than the emit buffer holds
+ * (it is sized for 8 x the expected bases/16^drlevel), the library grows the buffer and runs the affected scans again
+ * instead of failing -- the reference's unordered_set never fails on repeats (src/sketch.cpp:526-529). */
 int kssd_b200_sketch_scan_device(kssd_ctx *ctx, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
                                  const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg,
                                  uint64_t first_emit);
@@ -186,6 +189,13 @@ typedef struct kssd_hit { uint32_t row, col, common; } kssd_hit;
  * common > 0; the caller then knows that every unreported cell has common == 0, Jaccard 0 and distance 1
  * (dist_gpu.cpp fills them in, in reference order, where the threshold lets them pass).  Default: on = 1. */
 int kssd_b200_set_emit_zero_cells(kssd_ctx *ctx, int on);
+/* dist -N (src/dist.cpp:599, :625-640, :662-676: a bounded max-heap keeps the maxNeighbor smallest distances of a query
+ * row).  max_neighbor > 0 makes the device select per query row: only the max_neighbor cells with the smallest distances
+ * (plus everything tied with the last of them, to 2^-31 relative) among those that pass max_dist are reported -- per
+ * column tile when the references do not fit one tile, so the result is a SUPERSET of the row's top-N which the caller's
+ * exact heap (dist_gpu.cpp) finishes.  Cells with common == 0 are never candidates on the device: the caller fills them
+ * in when a row has fewer than max_neighbor reported cells and the threshold lets distance 1.0 pass.  0 = off (default). */
+int kssd_b200_set_max_neighbor(kssd_ctx *ctx, uint64_t max_neighbor);
 typedef int (*kssd_sink)(void *user, const kssd_hit *hits, size_t n);
 int kssd_b200_dist_rows(kssd_ctx *ctx, const uint32_t *q_hashes, const uint64_t *q_off, uint32_t n_query,
                         int ptr_kind, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size,

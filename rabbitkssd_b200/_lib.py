@@ -63,6 +63,7 @@ SYMBOLS = {
     "kssd_b200_index_adopt_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p,
                                                C.c_void_p, C.c_void_p]),
     "kssd_b200_set_emit_zero_cells": (C.c_int, [C.c_void_p, C.c_int]),
+    "kssd_b200_set_max_neighbor": (C.c_int, [C.c_void_p, C.c_uint64]),
     "kssd_b200_dist_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32,
                                       C.c_int, C.c_int, C.c_double, C.c_int, SINK, C.c_void_p]),
     "kssd_b200_dist_rows_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,

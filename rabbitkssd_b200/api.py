@@ -30,6 +30,7 @@ class Context:
         check(self.lib.kssd_b200_init(C.byref(self.h), device))
         self.params = None
         self.n_genomes = 0
+        self._keep = []  # host arrays the library may read again until sketch_finish (overflow replay)
 
     def close(self):
         if self.h:
@@ -81,6 +82,7 @@ class Context:
     def sketch_begin(self, n_genomes, has_qual=False, least_qual=0, least_num_kmer=1):
         check(self.lib.kssd_b200_sketch_begin(self.h, n_genomes, int(has_qual), least_qual, least_num_kmer))
         self.n_genomes = n_genomes
+        self._keep = []
 
     def submit_host(self, seq, seg_off, seg_genome, qual=None, first_emit=0):
         """One pinned batch: copies the arrays into a library-owned pinned batch and submits it (async)."""
@@ -117,6 +119,7 @@ class Context:
         """Stream a caller-owned (ideally pinned) host buffer through the double-buffered H2D pipeline."""
         seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)
         seg_genome = np.ascontiguousarray(seg_genome, dtype=np.uint32)
+        self._keep.append((seg_off, seg_genome))  # must stay valid until sketch_finish (include/kssd_b200.h)
         check(self.lib.kssd_b200_sketch_scan_host(self.h, C.c_void_p(seq_ptr), C.c_void_p(qual_ptr), n_bytes,
                                                   C.c_void_p(seg_off.ctypes.data), C.c_void_p(seg_genome.ctypes.data),
                                                   len(seg_genome), chunk_bytes))
@@ -236,6 +239,10 @@ class Context:
     # ---- distances ----
     def set_emit_zero_cells(self, on=True):
         check(self.lib.kssd_b200_set_emit_zero_cells(self.h, int(on)))
+
+    def set_max_neighbor(self, n):
+        """dist -N: the device reports per query row only the n smallest distances (+ ties); 0 = off."""
+        check(self.lib.kssd_b200_set_max_neighbor(self.h, int(n)))
 
     def dist_rows(self, q_hashes, q_off, triangle, kmer_size, max_dist, containment=0, rows=None):
         """-> structured hits (row, col, common) that pass the device's conservative test (host refines)."""

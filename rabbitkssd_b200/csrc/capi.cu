@@ -158,7 +158,7 @@ void kssd_b200_destroy(kssd_ctx *c) {
                      &c->d_q_off, &c->d_q_list_begin, &c->d_q_list_end, &c->d_hits, &c->d_hit_cursor, &c->d_rowwork, &c->d_gcount, &c->d_seg_start, &c->d_ucount,
                      &c->d_emit_rank, &c->d_cat_hashes, &c->d_cat_off, &c->d_cat_counts};
     for (DevBuf *b : dev) b->release();
-    HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits};
+    HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits, &c->h_snap};
     for (HostBuf *b : host) b->release();
     for (int i = 0; i < 2; i++) {
         c->bpriv[i].seq.release();

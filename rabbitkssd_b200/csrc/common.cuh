@@ -58,6 +58,20 @@ struct ScanParams {
     int dim_end;
 };
 
+// One scan submitted in the current sketch session whose keys are not yet known to have fit the emit buffer.  When the
+// buffer overflows (repeat-rich input), the unverified scans are undone and run again into a grown buffer
+// (capi_sketch.inc: verify_scans); the reference never fails on repeats (src/sketch.cpp:526-529).
+struct ReplayItem {
+    int kind;            // 0: device buffers (a staged batch or the caller's resident buffer), 1: the caller's host buffers (scan_host)
+    int stage;           // staging buffer the scan read (-1: none)
+    const uint8_t *seq, *qual;
+    uint64_t n_bytes;
+    const uint64_t *seg_off;
+    const uint32_t *seg_genome;
+    uint32_t n_seg;
+    uint64_t first_emit, chunk_bytes;
+};
+
 struct TimedLaunches {
     std::vector<cudaEvent_t> ev;  // pairs
     std::vector<cudaEvent_t> pool;
@@ -108,6 +122,10 @@ struct kssd_ctx {
     uint32_t n_genomes = 0;
     int has_qual = 0, least_qual = 0, least_num_kmer = 1;
     uint64_t bases_submitted = 0;
+    std::vector<kssd::ReplayItem> replay;  // scans not yet verified against the emit capacity, in submission order
+    uint64_t verified_cursor = 0;          // emit cursor after the last verified scan
+    bool replaying = false;
+    kssd::HostBuf h_snap;                  // pinned: emit cursor after the last scan of staging buffer 0 / 1
     kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
     kssd::DevBuf d_emit_rank; // u32 rank of each key inside its genome
     uint64_t emit_cap = 0;
@@ -132,6 +150,7 @@ struct kssd_ctx {
 
     // index (CSR over distinct hashes)
     bool have_index = false;
+    bool hash64 = false;       // d_uniq_hash / sketches hold 64-bit hashes (half_k - drlevel > 8, src/sketch.cpp:336)
     uint64_t n_uniq = 0, n_post = 0;
     uint32_t n_ref = 0;
     uint32_t max_ref_size = 0;
@@ -143,7 +162,10 @@ struct kssd_ctx {
 
     // distances
     bool emit_zero_cells = true;  // report cells with common == 0 when they pass the threshold (kssd_b200_set_emit_zero_cells)
-    kssd::DevBuf d_q_hashes, d_q_off, d_q_list_begin, d_q_list_end, d_hits, d_hit_cursor, d_rowwork;
+    uint64_t max_neighbor = 0;    // > 0: dist reports only the top-N cells of a row (kssd_b200_set_max_neighbor)
+    kssd::DevBuf d_q_hashes, d_q_off, d_hits, d_hit_cursor, d_rowwork;
+    kssd::DevBuf d_q_list_begin;  // alldist: posting ranges per row (uint2 begin, end), slots of row g at q_off[g]
+    kssd::DevBuf d_q_list_end;    // alldist: ranges filled per row
     kssd::HostBuf h_hits;
 
     kssd::TimedLaunches t_scan, t_count;
@@ -181,7 +203,7 @@ int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_word
                       int *overflow);
 int index_build_buckets(kssd_ctx *c, int64_t known_max_hash = -1);  // after d_uniq_hash / n_uniq are in place
 // dist.cu
-int dist_rows_device(kssd_ctx *c, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
+int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
                      uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
                      int containment, uint64_t *n_hits);
 }  // namespace kssd

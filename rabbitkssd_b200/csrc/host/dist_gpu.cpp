@@ -227,7 +227,11 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
     std::vector<kssd_hit> hits;
     check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
     const bool dense = 1.0 < maxDist;  // zero cells pass `mashD < maxDist` (dist.cpp:227-232)
-    check(kssd_b200_dist_rows(ctx, flat.data(), off.data(), (uint32_t)numRef, KSSD_PTR_HOST, 0, (uint32_t)numRef, 1, kmer_size, maxDist,
+    // dense: every unreported cell is printed as a zero cell, so the device must report EVERY cell with common > 0
+    // (threshold +inf); the exact test below drops the ones whose distance does not pass
+    const double devDist = dense ? INFINITY : maxDist;
+    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
+    check(kssd_b200_dist_rows(ctx, flat.data(), off.data(), (uint32_t)numRef, KSSD_PTR_HOST, 0, (uint32_t)numRef, 1, kmer_size, devDist,
                               isContainment, collect_hits, &hits),
           "dist_rows");
     std::vector<size_t> row_begin;
@@ -257,6 +261,7 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
         }
         fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
     }
+    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
     const double t2 = get_sec();
     std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
     sub.finish();
@@ -289,12 +294,16 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
     const size_t numRef = ref_sketches.size();
     check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
     const bool dense = 1.0 <= maxDist;  // zero cells pass `mashD <= maxDist` (dist.cpp:621-624)
+    const double devDist = dense ? INFINITY : maxDist;  // dense: the device reports every cell with common > 0 (see index_tridist)
+    // -N: the device selects the maxNeighbor smallest distances (+ ties) of every row among the cells with common > 0;
+    // the bounded max-heap below (dist.cpp:625-640) runs over that superset
+    check(kssd_b200_set_max_neighbor(ctx, isNeighbor ? maxNeighbor : 0), "set_max_neighbor");
     const size_t block = std::max<size_t>(1, std::min<size_t>(numQuery ? numQuery : 1, (size_t)(64u << 20) / std::max<size_t>(numRef, 1)));
     for (size_t q0 = 0; q0 < numQuery; q0 += block) {
         const size_t q1 = std::min(numQuery, q0 + block);
         std::vector<kssd_hit> hits;
         check(kssd_b200_dist_rows(ctx, qflat.data(), qoff.data(), (uint32_t)numQuery, KSSD_PTR_HOST, (uint32_t)q0, (uint32_t)q1, 0, kmer_size,
-                                  maxDist, isContainment, collect_hits, &hits),
+                                  devDist, isContainment, collect_hits, &hits),
               "dist_rows");
         std::vector<size_t> row_begin;
         group_by_row(hits, numQuery, row_begin);
@@ -305,7 +314,7 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
                 fprintf(sub.fpIndexArr[t], "%s\t%s\n", query_sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
                 const int size1 = (int)qsizes[i];
                 priority_queue<DistInfo, vector<DistInfo>, cmpDistInfo> curQueue;  // dist.cpp:599
-                for_each_cell(hits, row_begin[i], row_begin[i + 1], 0, numRef, dense, [&](size_t j, int common) {  // ascending ref index
+                auto offer = [&](size_t j, int common) {  // one cell of the reference's j loop (dist.cpp:600-681)
                     const int size0 = (int)rsizes[j];
                     double jorc, d;
                     exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
@@ -330,7 +339,25 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
                             strBuf.clear();
                         }
                     }
-                });
+                };
+                if (!isNeighbor) {
+                    for_each_cell(hits, row_begin[i], row_begin[i + 1], 0, numRef, dense, offer);  // ascending ref index
+                } else if (maxNeighbor > 0) {
+                    // The same heap operations as the reference's j loop, without walking all numRef columns: a zero cell
+                    // (distance exactly 1.0) changes the heap only while it is not full or while its top is > 1.0, so the
+                    // columns between two reported cells are visited only until then.
+                    size_t j = 0;
+                    for (size_t k = row_begin[i]; k <= row_begin[i + 1]; k++) {
+                        const size_t stop = k < row_begin[i + 1] ? (size_t)hits[k].col : numRef;
+                        if (dense)
+                            for (; j < stop; j++) {
+                                if (curQueue.size() >= maxNeighbor && !(1.0 < curQueue.top().dist)) break;
+                                offer(j, 0);
+                            }
+                        if (k < row_begin[i + 1]) offer(stop, (int)hits[k].common);
+                        j = stop + 1;
+                    }
+                }
                 while (!curQueue.empty()) {  // drained largest first, dist.cpp:683-689
                     const DistInfo di = curQueue.top();
                     strBuf += query_sketches[i].fileName + '\t' + di.refName + '\t' + to_string(di.common) + '|' + to_string(di.refSize) + '|' +
@@ -345,6 +372,7 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
             fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
         }
     }
+    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
     const double t2 = get_sec();
     std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
     sub.finish();
