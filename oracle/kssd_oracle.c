@@ -383,3 +383,74 @@ uint64_t kssd_oracle_dist(const uint32_t *q_hashes, const uint64_t *q_off, uint3
     }
     return total;
 }
+
+/* ---- synthetic inputs for the CPU legs of bench.py (not part of the restated algorithm) -------------------------
+ * The same genomes rabbitkssd_b200/synth.py:family() and synth.family_device() generate (counter-based splitmix64:
+ * base genome = 2 bits per base from the stream of `seed`; member m = base with i.i.d. substitutions at rate
+ * max_div * m / (n_members - 1) drawn from the stream of seed * 1000003 + m), written as FASTA files so that the
+ * reference binary can be timed on exactly the workload the GPU arm runs. */
+static inline uint64_t splitmix_at(uint64_t seed, uint64_t counter)
+{
+    uint64_t z = counter * 0x9E3779B97F4A7C15ULL + seed;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+void kssd_oracle_synth_genome(uint64_t seed, int member, int n_members, uint64_t length, double max_div, uint8_t *out)
+{
+    static const char acgt[4] = {'A', 'C', 'G', 'T'};
+    const uint64_t seed2 = seed * 1000003ULL + (uint64_t)member;
+    const double rate = member ? max_div * (double)member / (double)(n_members > 1 ? n_members - 1 : 1) : 0.0;
+    const uint64_t thresh = (uint64_t)(rate * 9007199254740992.0); /* int(rate * 2.0 ** 53) */
+    for (uint64_t w = 0; w * 32 < length; w++) {
+        const uint64_t r = splitmix_at(seed, w + 1);
+        const uint64_t end = (w + 1) * 32 < length ? (w + 1) * 32 : length;
+        for (uint64_t i = w * 32; i < end; i++) {
+            unsigned code = (unsigned)(r >> (2 * (i - w * 32))) & 3u;
+            if (member) {
+                const uint64_t m = splitmix_at(seed2, i + 1);
+                if ((m >> 11) < thresh) code = (code + (unsigned)((m & 0x7FF) % 3) + 1u) & 3u;
+            }
+            out[i] = (uint8_t)acgt[code];
+        }
+    }
+}
+
+/* Writes genomes [first, first + n) of the family series (family f = index / n_members has seed seed0 + 101 * f) as
+ * <dir>/g<index>.fna: n_contigs records "<name>_<c> synthetic", 80-column lines (synth.write_fasta).  Returns the
+ * number of files written, < n on an I/O error. */
+int kssd_oracle_synth_fasta_files(const char *dir, uint64_t seed0, uint32_t first, uint32_t n, int n_members, uint64_t length,
+                                  double max_div, int n_contigs)
+{
+    int written = 0;
+#pragma omp parallel for schedule(dynamic) reduction(+ : written)
+    for (uint32_t q = 0; q < n; q++) {
+        const uint32_t g = first + q;
+        uint8_t *buf = (uint8_t *)malloc(length + 1);
+        char path[4096];
+        snprintf(path, sizeof(path), "%s/g%u.fna", dir, g);
+        FILE *f = buf ? fopen(path, "wb") : NULL;
+        if (!f) { free(buf); continue; }
+        kssd_oracle_synth_genome(seed0 + 101ULL * (g / (uint32_t)n_members), (int)(g % (uint32_t)n_members), n_members, length, max_div, buf);
+        char *line = (char *)malloc((size_t)(length + length / 80 + 2));
+        int ok = line != NULL;
+        for (int c = 0; ok && c < n_contigs; c++) {
+            const uint64_t b0 = length * (uint64_t)c / (uint64_t)n_contigs, b1 = length * (uint64_t)(c + 1) / (uint64_t)n_contigs;
+            fprintf(f, ">g%u.fna_%d synthetic\n", g, c);
+            size_t o = 0;
+            for (uint64_t i = b0; i < b1; i += 80) {
+                const uint64_t e = i + 80 < b1 ? i + 80 : b1;
+                memcpy(line + o, buf + i, e - i);
+                o += e - i;
+                line[o++] = '\n';
+            }
+            ok = fwrite(line, 1, o, f) == o;
+        }
+        free(line);
+        ok = (fclose(f) == 0) && ok;
+        free(buf);
+        written += ok;
+    }
+    return written;
+}

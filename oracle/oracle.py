@@ -67,6 +67,11 @@ def lib():
                                        u32p, u64p, C.c_uint64, u32p, C.c_int, C.c_double, C.c_int,
                                        u32p, u32p, u32p, C.c_uint64]
         L.kssd_oracle_dist.restype = C.c_uint64
+        L.kssd_oracle_synth_genome.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_uint64, C.c_double, u8p]
+        L.kssd_oracle_synth_genome.restype = None
+        L.kssd_oracle_synth_fasta_files.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_uint64,
+                                                    C.c_double, C.c_int]
+        L.kssd_oracle_synth_fasta_files.restype = C.c_int
         _LIB = L
     return _LIB
 
@@ -184,3 +189,18 @@ def dist(q_hashes, q_off, r_hashes, r_off, kmer_size, max_dist, is_containment=0
     tot = lib().kssd_oracle_dist(*args, _p(hr, C.c_uint32), _p(hc, C.c_uint32), _p(hm, C.c_uint32), cap)
     o = np.lexsort((hc[:tot], hr[:tot]))
     return hr[:tot][o], hc[:tot][o], hm[:tot][o]
+
+
+def synth_genome(seed, member, n_members, length, max_div=0.04):
+    """ASCII bases of one member of a synthetic family: the bytes rabbitkssd_b200.synth.family() generates."""
+    out = np.empty(length, dtype=np.uint8)
+    lib().kssd_oracle_synth_genome(seed & 0xFFFFFFFFFFFFFFFF, member, n_members, length, max_div, _p(out, C.c_uint8))
+    return out
+
+
+def synth_fasta_files(directory, seed0, first, n, n_members, length, max_div=0.04, n_contigs=2):
+    """Writes genomes [first, first+n) of the bench's family series as <directory>/g<i>.fna (OpenMP over files)."""
+    got = lib().kssd_oracle_synth_fasta_files(directory.encode(), seed0 & 0xFFFFFFFFFFFFFFFF, first, n, n_members, length,
+                                              max_div, n_contigs)
+    if got != n:
+        raise OSError(f"synth_fasta_files: wrote {got} of {n} files into {directory}")

@@ -157,3 +157,38 @@ def synth_sketches(seed, n_clusters, cluster_size, sketch_size, hash_bits, survi
             offs.append(offs[-1] + len(h))
     hashes = np.concatenate(chunks) if chunks else np.zeros(0, np.uint32)
     return hashes, np.asarray(offs, dtype=np.uint64)
+
+
+# ---- the same generator on a CUDA device (bench.py: genomes generated straight into HBM) ---------------------------
+def _i64(v):
+    v &= 0xFFFFFFFFFFFFFFFF
+    return v - (1 << 64) if v >= (1 << 63) else v
+
+
+def _splitmix64_torch(torch, seed, n, device):
+    """splitmix64(seed, n) as int64 bit patterns (torch has no uint64 arithmetic: multiplies wrap, shifts are made logical)."""
+    z = torch.arange(1, n + 1, dtype=torch.int64, device=device) * _i64(0x9E3779B97F4A7C15) + _i64(seed)
+    z = (z ^ ((z >> 30) & ((1 << 34) - 1))) * _i64(0xBF58476D1CE4E5B9)
+    z = (z ^ ((z >> 27) & ((1 << 37) - 1))) * _i64(0x94D049BB133111EB)
+    return z ^ ((z >> 31) & ((1 << 33) - 1))
+
+
+def family_device(torch, seed, n_members, length, max_div=0.04, device="cuda"):
+    """family(seed, n_members, length, max_div) on the device: list of uint8 ASCII tensors (one per member, contigs not
+    cut), byte-identical to the numpy generator."""
+    lut = torch.tensor(list(b"ACGT"), dtype=torch.uint8, device=device)
+    r = _splitmix64_torch(torch, seed, (length + 31) // 32, device)
+    sh = torch.arange(32, dtype=torch.int64, device=device) * 2
+    base = ((r[:, None] >> sh[None, :]) & 3).reshape(-1)[:length]
+    out = []
+    for m in range(n_members):
+        codes = base
+        if m:
+            rate = max_div * m / max(1, n_members - 1)
+            thresh = int(rate * 2.0 ** 53)
+            q = _splitmix64_torch(torch, seed * 1000003 + m, length, device)
+            hit = ((q >> 11) & ((1 << 53) - 1)) < thresh
+            shift = (q & 0x7FF) % 3 + 1
+            codes = torch.where(hit, (base + shift) & 3, base)
+        out.append(lut[codes])
+    return out
