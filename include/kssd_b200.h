@@ -11,8 +11,9 @@
  *    library never calls exit(); there is NO CPU fallback: without a usable CUDA device init fails.
  *  - one kssd_ctx per GPU (one process or one host thread per GPU); a ctx is not thread-safe.
  *  - pointers are HOST pointers unless the parameter is named d_* or the call ends in _device.
- *  - hashes are uint32 (the reference's 32-bit path, half_k - drlevel <= 8, sketch.cpp:336); the 64-bit
- *    path is reported as KSSD_E_UNSUPPORTED.
+ *  - hashes are uint32 when half_k - drlevel <= 8 and uint64 otherwise (sketch.cpp:336 use64); set_params decides,
+ *    and the entry points that carry hashes come in two widths (the *64 ones for the 64-bit configuration).
+ *    Calling the wrong width returns KSSD_E_ARG.
  */
 #ifndef KSSD_B200_H
 #define KSSD_B200_H
@@ -26,7 +27,7 @@ extern "C" {
 #define KSSD_OK 0
 #define KSSD_E_CUDA (-1)        /* CUDA runtime error (text has the cudaError string) */
 #define KSSD_E_ARG (-2)         /* bad argument / call order */
-#define KSSD_E_UNSUPPORTED (-3) /* configuration the library does not implement (64-bit hashes) */
+#define KSSD_E_UNSUPPORTED (-3) /* shape the library does not implement (half_k > 12, >= 2^32 postings); the text says which */
 #define KSSD_E_PARAM (-4)       /* half_subk - drlevel < 3: the reference aborts here (common.cpp:37-39) */
 #define KSSD_E_OVERFLOW (-5)    /* an output buffer stayed too small after regrowing; text says which and the size needed */
 
@@ -54,6 +55,10 @@ int kssd_b200_sync(kssd_ctx *ctx);
  * :616-623).  shuffled_dim = the 16^half_subk ints of the .shuf file (src/shuffle.cpp:8-23), borrowed for
  * the call.  Uploads the masks, a symmetrised membership bitmap and the exact retained-subset table. */
 int kssd_b200_set_params(kssd_ctx *ctx, int half_k, int half_subk, int drlevel, const int32_t *shuffled_dim);
+/* on = 1: set_params accepts half_subk - drlevel < 3 (still > 0), which the reference refuses (common.cpp:37-39,
+ * shuffle.cpp:30-33) -- BASELINE config 4 names L5K10 (half_subk 7, drlevel 5).  There is no reference output for such a
+ * configuration; the arithmetic is the same.  Default 0: KSSD_E_PARAM with the reference's message. */
+int kssd_b200_set_relax_guard(kssd_ctx *ctx, int on);
 
 /* ---- sketching --------------------------------------------------------------------------------------
  * replaces the per-base scan + per-genome set of sketchFastaFile / sketchFastqFile and the consumer tasks
@@ -106,6 +111,11 @@ int kssd_b200_sketch_finish(kssd_ctx *ctx, const uint32_t **hashes, const uint64
 /* Same, results stay in device memory (library owned). */
 int kssd_b200_sketch_finish_device(kssd_ctx *ctx, const uint32_t **d_hashes, const uint64_t **d_genome_off,
                                    uint64_t *total);
+/* 64-bit hash configuration (half_k - drlevel > 8: sketch.cpp:336, hashSet64 of sketch_t, sketch.h:22): the same
+ * session calls, hashes come out as uint64. */
+int kssd_b200_sketch_finish64(kssd_ctx *ctx, const uint64_t **hashes, const uint64_t **genome_off);
+int kssd_b200_sketch_finish_device64(kssd_ctx *ctx, const uint64_t **d_hashes, const uint64_t **d_genome_off,
+                                     uint64_t *total);
 /* Multi-GPU gather epilogue (the sketch shards of all ranks are all-gathered before the index is
  * built; the reference has one address space, its counterpart is the `sketches` vector filled under omp critical,
  * src/sketch.cpp:455-560).  d_parts (device) holds `world` blocks of stride_words u32 each, block r =
@@ -144,6 +154,17 @@ int kssd_b200_index_build(kssd_ctx *ctx, const uint32_t *hashes, const uint64_t 
                           int ptr_kind);
 int kssd_b200_index_export(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, const uint32_t **uniq_hash,
                            const uint32_t **uniq_count, const uint32_t **dict);
+/* 64-bit hash configuration: replaces transSketches' hash-map path (src/sketch.cpp:904-969).  index_export64 returns the
+ * content of the sparse .index file (size_t n; uint64 hash[n]; uint32 count[n], sketch.cpp:951-958) and of .dict, lists
+ * in ASCENDING hash order (the reference writes its hash map's iteration order; readers rebuild a map, dist.cpp:45-78). */
+int kssd_b200_index_build64(kssd_ctx *ctx, const uint64_t *hashes, const uint64_t *genome_off, uint32_t n_genomes,
+                            int ptr_kind);
+int kssd_b200_index_export64(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, const uint64_t **uniq_hash,
+                             const uint32_t **uniq_count, const uint32_t **dict);
+/* replaces the 64-bit .index/.dict load of index_tridist / index_dist (src/dist.cpp:35-82, :442-487): n_hash (hash,
+ * count) entries in ANY order, dict = the posting lists in the same order. */
+int kssd_b200_index_load64(kssd_ctx *ctx, uint64_t n_hash, const uint64_t *hash, const uint32_t *counts,
+                           const uint32_t *dict, uint64_t total, const uint32_t *ref_sizes, uint32_t n_ref);
 /* replaces the .index/.dict load + prefix sum of index_tridist / index_dist (src/dist.cpp:83-130, :488-523):
  * counts = the dense count array of the .index file (hash_size entries), dict = the .dict payload. */
 int kssd_b200_index_load(kssd_ctx *ctx, uint64_t hash_size, const uint32_t *counts, const uint32_t *dict,
@@ -205,6 +226,16 @@ int kssd_b200_dist_rows_device(kssd_ctx *ctx, const uint32_t *d_q_hashes, const 
                                uint32_t n_query, uint32_t row_begin, uint32_t row_end, int triangle,
                                int kmer_size, double max_dist, int containment, const kssd_hit **d_hits,
                                uint64_t *n_hits);
+
+/* 64-bit hash configuration (src/dist.cpp:180-192, :566-576): query hashes are uint64, the index was built / loaded by
+ * the *64 entry points.  Everything else as above. */
+int kssd_b200_dist_rows64(kssd_ctx *ctx, const uint64_t *q_hashes, const uint64_t *q_off, uint32_t n_query,
+                          int ptr_kind, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size,
+                          double max_dist, int containment, kssd_sink sink, void *user);
+int kssd_b200_dist_rows_device64(kssd_ctx *ctx, const uint64_t *d_q_hashes, const uint64_t *d_q_off,
+                                 uint32_t n_query, uint32_t row_begin, uint32_t row_end, int triangle,
+                                 int kmer_size, double max_dist, int containment, const kssd_hit **d_hits,
+                                 uint64_t *n_hits);
 
 /* ---- introspection for bench.py / tests ---------------------------------------------------------------- */
 /* Bracket the scan / count kernels with CUDA events on the ctx stream (off by default). */

@@ -68,6 +68,16 @@ SYMBOLS = {
                                       C.c_int, C.c_int, C.c_double, C.c_int, SINK, C.c_void_p]),
     "kssd_b200_dist_rows_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                              C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_void_p), u64p]),
+    "kssd_b200_set_relax_guard": (C.c_int, [C.c_void_p, C.c_int]),
+    "kssd_b200_sketch_finish64": (C.c_int, [C.c_void_p, C.POINTER(u64p), C.POINTER(u64p)]),
+    "kssd_b200_sketch_finish_device64": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), u64p]),
+    "kssd_b200_index_build64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]),
+    "kssd_b200_index_export64": (C.c_int, [C.c_void_p, u64p, u64p, C.POINTER(u64p), C.POINTER(u32p), C.POINTER(u32p)]),
+    "kssd_b200_index_load64": (C.c_int, [C.c_void_p, C.c_uint64, u64p, u32p, u32p, C.c_uint64, u32p, C.c_uint32]),
+    "kssd_b200_dist_rows64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32,
+                                        C.c_int, C.c_int, C.c_double, C.c_int, SINK, C.c_void_p]),
+    "kssd_b200_dist_rows_device64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                               C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_void_p), u64p]),
     "kssd_b200_launch_count": (C.c_uint64, [C.c_void_p]),
     "kssd_b200_scan_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p]),
     "kssd_b200_count_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p, u64p]),

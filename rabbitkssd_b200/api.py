@@ -29,6 +29,8 @@ class Context:
         self.h = C.c_void_p()
         check(self.lib.kssd_b200_init(C.byref(self.h), device))
         self.params = None
+        self.hash64 = False     # the parameters select 64-bit hashes (half_k - drlevel > 8, src/sketch.cpp:336)
+        self.index64 = False    # the loaded index holds 64-bit hashes
         self.n_genomes = 0
         self._keep = []  # host arrays the library may read again until sketch_finish (overflow replay)
 
@@ -52,6 +54,10 @@ class Context:
 
     def set_profiling(self, on=True):
         check(self.lib.kssd_b200_set_profiling(self.h, int(on)))
+
+    def set_relax_guard(self, on=True):
+        """Accept half_subk - drlevel < 3 (L5K10), which the reference refuses (src/common.cpp:37-39)."""
+        check(self.lib.kssd_b200_set_relax_guard(self.h, int(on)))
 
     def set_force_radix(self, on=True):
         """Tests: take the device-wide radix paths even where the shared-memory segment sorts apply."""
@@ -77,6 +83,7 @@ class Context:
             raise ValueError("shuffled_dim must have 16^half_subk entries")
         check(self.lib.kssd_b200_set_params(self.h, half_k, half_subk, drlevel, dim.ctypes.data_as(_lib.i32p)))
         self.params = (half_k, half_subk, drlevel)
+        self.hash64 = half_k - drlevel > 8
 
     # ---- sketching ----
     def sketch_begin(self, n_genomes, has_qual=False, least_qual=0, least_num_kmer=1):
@@ -126,6 +133,11 @@ class Context:
 
     def sketch_finish(self):
         """-> (hashes uint32[total], genome_off uint64[n_genomes+1]) on the host; per genome sorted unique."""
+        if self.hash64:  # uint64 hashes
+            hp, op = _lib.u64p(), _lib.u64p()
+            check(self.lib.kssd_b200_sketch_finish64(self.h, C.byref(hp), C.byref(op)))
+            off = _np_from_ptr(op, self.n_genomes + 1, np.uint64)
+            return _np_from_ptr(hp, int(off[-1]), np.uint64), off
         hp, op = _lib.u32p(), _lib.u64p()
         check(self.lib.kssd_b200_sketch_finish(self.h, C.byref(hp), C.byref(op)))
         off = _np_from_ptr(op, self.n_genomes + 1, np.uint64)
@@ -134,7 +146,8 @@ class Context:
     def sketch_finish_device(self):
         """-> (d_hashes ptr, d_genome_off ptr, total); library-owned device memory."""
         hp, op, tot = C.c_void_p(), C.c_void_p(), C.c_uint64()
-        check(self.lib.kssd_b200_sketch_finish_device(self.h, C.byref(hp), C.byref(op), C.byref(tot)))
+        fn = self.lib.kssd_b200_sketch_finish_device64 if self.hash64 else self.lib.kssd_b200_sketch_finish_device
+        check(fn(self.h, C.byref(hp), C.byref(op), C.byref(tot)))
         return hp.value or 0, op.value or 0, tot.value
 
     def sketch_concat_device(self, d_parts, stride_words, n_local, world):
@@ -187,13 +200,19 @@ class Context:
 
     # ---- index ----
     def index_build(self, hashes, genome_off):
-        hashes = np.ascontiguousarray(hashes, dtype=np.uint32)
+        """hashes: uint32, or uint64 for the 64-bit hash configuration (the dtype decides)."""
+        hashes = np.ascontiguousarray(hashes)
+        self.index64 = hashes.dtype == np.uint64
+        if not self.index64:
+            hashes = np.ascontiguousarray(hashes, dtype=np.uint32)
         genome_off = np.ascontiguousarray(genome_off, dtype=np.uint64)
-        check(self.lib.kssd_b200_index_build(self.h, C.c_void_p(hashes.ctypes.data), C.c_void_p(genome_off.ctypes.data),
-                                             len(genome_off) - 1, 0))
+        fn = self.lib.kssd_b200_index_build64 if self.index64 else self.lib.kssd_b200_index_build
+        check(fn(self.h, C.c_void_p(hashes.ctypes.data), C.c_void_p(genome_off.ctypes.data), len(genome_off) - 1, 0))
 
-    def index_build_device(self, d_hashes, d_genome_off, n_genomes):
-        check(self.lib.kssd_b200_index_build(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1))
+    def index_build_device(self, d_hashes, d_genome_off, n_genomes, hash64=False):
+        self.index64 = bool(hash64)
+        fn = self.lib.kssd_b200_index_build64 if hash64 else self.lib.kssd_b200_index_build
+        check(fn(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1))
 
     def index_build_range(self, d_hashes, d_genome_off, n_genomes, part, parts, d_block, block_words):
         """CSR of hash range `part` of `parts` packed into the caller's device block -> (overflow flag, words used)."""
@@ -209,12 +228,24 @@ class Context:
         return bool(ov.value)
 
     def index_export(self):
-        """-> (uniq_hash u32[U], uniq_count u32[U], dict u32[P])"""
+        """-> (uniq_hash u32[U] (u64 for a 64-bit index), uniq_count u32[U], dict u32[P]), ascending hash order"""
         U, P = C.c_uint64(), C.c_uint64()
-        uh, uc, dc = _lib.u32p(), _lib.u32p(), _lib.u32p()
-        check(self.lib.kssd_b200_index_export(self.h, C.byref(U), C.byref(P), C.byref(uh), C.byref(uc), C.byref(dc)))
-        return (_np_from_ptr(uh, U.value, np.uint32), _np_from_ptr(uc, U.value, np.uint32),
+        uh, uc, dc = (_lib.u64p() if self.index64 else _lib.u32p()), _lib.u32p(), _lib.u32p()
+        fn = self.lib.kssd_b200_index_export64 if self.index64 else self.lib.kssd_b200_index_export
+        check(fn(self.h, C.byref(U), C.byref(P), C.byref(uh), C.byref(uc), C.byref(dc)))
+        return (_np_from_ptr(uh, U.value, np.uint64 if self.index64 else np.uint32), _np_from_ptr(uc, U.value, np.uint32),
                 _np_from_ptr(dc, P.value, np.uint32))
+
+    def index_load64(self, hashes, counts, postings, ref_sizes):
+        """The content of the 64-bit .index / .dict files (formats.read_index_dict64), any hash order."""
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
+        counts = np.ascontiguousarray(counts, dtype=np.uint32)
+        postings = np.ascontiguousarray(postings, dtype=np.uint32)
+        ref_sizes = np.ascontiguousarray(ref_sizes, dtype=np.uint32)
+        check(self.lib.kssd_b200_index_load64(self.h, len(hashes), hashes.ctypes.data_as(_lib.u64p), counts.ctypes.data_as(_lib.u32p),
+                                              postings.ctypes.data_as(_lib.u32p), len(postings),
+                                              ref_sizes.ctypes.data_as(_lib.u32p), len(ref_sizes)))
+        self.index64 = True
 
     def index_load(self, counts, postings, ref_sizes):
         counts = np.ascontiguousarray(counts, dtype=np.uint32)
@@ -223,6 +254,7 @@ class Context:
         check(self.lib.kssd_b200_index_load(self.h, len(counts), counts.ctypes.data_as(_lib.u32p),
                                             postings.ctypes.data_as(_lib.u32p), len(postings),
                                             ref_sizes.ctypes.data_as(_lib.u32p), len(ref_sizes)))
+        self.index64 = False
 
     def index_device_views(self):
         U, P, N = C.c_uint64(), C.c_uint64(), C.c_uint32()
@@ -246,7 +278,7 @@ class Context:
 
     def dist_rows(self, q_hashes, q_off, triangle, kmer_size, max_dist, containment=0, rows=None):
         """-> structured hits (row, col, common) that pass the device's conservative test (host refines)."""
-        q_hashes = np.ascontiguousarray(q_hashes, dtype=np.uint32)
+        q_hashes = np.ascontiguousarray(q_hashes, dtype=np.uint64 if self.index64 else np.uint32)
         q_off = np.ascontiguousarray(q_off, dtype=np.uint64)
         nq = len(q_off) - 1
         r0, r1 = (0, nq) if rows is None else rows
@@ -258,8 +290,9 @@ class Context:
             return 0
 
         cb = _lib.SINK(sink)
-        check(self.lib.kssd_b200_dist_rows(self.h, C.c_void_p(q_hashes.ctypes.data), C.c_void_p(q_off.ctypes.data), nq, 0,
-                                           r0, r1, int(triangle), kmer_size, float(max_dist), int(containment), cb, None))
+        fn = self.lib.kssd_b200_dist_rows64 if self.index64 else self.lib.kssd_b200_dist_rows
+        check(fn(self.h, C.c_void_p(q_hashes.ctypes.data), C.c_void_p(q_off.ctypes.data), nq, 0,
+                 r0, r1, int(triangle), kmer_size, float(max_dist), int(containment), cb, None))
         if not chunks:
             return np.zeros((0, 3), dtype=np.uint32)
         return np.concatenate(chunks)
@@ -267,9 +300,9 @@ class Context:
     def dist_rows_device(self, d_q_hashes, d_q_off, n_query, triangle, kmer_size, max_dist, containment=0, rows=None):
         r0, r1 = (0, n_query) if rows is None else rows
         hp, n = C.c_void_p(), C.c_uint64()
-        check(self.lib.kssd_b200_dist_rows_device(self.h, C.c_void_p(d_q_hashes), C.c_void_p(d_q_off), n_query, r0, r1,
-                                                  int(triangle), kmer_size, float(max_dist), int(containment),
-                                                  C.byref(hp), C.byref(n)))
+        fn = self.lib.kssd_b200_dist_rows_device64 if self.index64 else self.lib.kssd_b200_dist_rows_device
+        check(fn(self.h, C.c_void_p(d_q_hashes), C.c_void_p(d_q_off), n_query, r0, r1,
+                 int(triangle), kmer_size, float(max_dist), int(containment), C.byref(hp), C.byref(n)))
         return hp.value or 0, n.value
 
 

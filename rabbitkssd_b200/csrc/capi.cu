@@ -156,9 +156,10 @@ void kssd_b200_destroy(kssd_ctx *c) {
                      &c->d_stage_seggen[1], &c->d_sort_tmp, &c->d_sort_counts, &c->d_keys_unique, &c->d_hashes, &c->d_genome_off,
                      &c->d_uniq_hash, &c->d_uniq_off, &c->d_dict, &c->d_ref_sizes, &c->d_pairs, &c->d_pairs_tmp, &c->d_bucket, &c->d_q_hashes,
                      &c->d_q_off, &c->d_q_list_begin, &c->d_q_list_end, &c->d_hits, &c->d_hit_cursor, &c->d_rowwork, &c->d_gcount, &c->d_seg_start, &c->d_ucount,
-                     &c->d_emit_rank, &c->d_cat_hashes, &c->d_cat_off, &c->d_cat_counts};
+                     &c->d_emit_rank, &c->d_cat_hashes, &c->d_cat_off, &c->d_cat_counts, &c->d_emit_gen, &c->d_h64_a, &c->d_h64_b, &c->d_dict64,
+                     &c->d_hashes64, &c->d_uniq_hash64, &c->d_ranks};
     for (DevBuf *b : dev) b->release();
-    HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits, &c->h_snap};
+    HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits, &c->h_snap, &c->h_hashes64, &c->h_uniq_hash64};
     for (HostBuf *b : host) b->release();
     for (int i = 0; i < 2; i++) {
         c->bpriv[i].seq.release();
@@ -201,6 +202,12 @@ int kssd_b200_set_profiling(kssd_ctx *c, int on) {
     return KSSD_OK;
 }
 
+int kssd_b200_set_relax_guard(kssd_ctx *c, int on) {
+    KSSD_TRY(check_ctx(c));
+    c->relax_guard = on != 0;
+    return KSSD_OK;
+}
+
 int kssd_b200_set_force_radix(kssd_ctx *c, int on) {
     KSSD_TRY(check_ctx(c));
     c->force_radix = on != 0;
@@ -210,18 +217,15 @@ int kssd_b200_set_force_radix(kssd_ctx *c, int on) {
 int kssd_b200_set_params(kssd_ctx *c, int half_k, int half_subk, int drlevel, const int32_t *shuffled_dim) {
     KSSD_TRY(check_ctx(c));
     if (!shuffled_dim) { set_error("set_params: null shuffle table"); return KSSD_E_ARG; }
-    if (half_subk - drlevel < 3) {  // common.cpp:37-39
+    if (half_subk - drlevel < 3 && !c->relax_guard) {  // common.cpp:37-39
         set_error("the half_subk - drlevel should at least 3; current half_subk and drlevel are: %d and %d", half_subk, drlevel);
         return KSSD_E_PARAM;
     }
-    if (half_k < half_subk || half_subk < 1 || half_subk >= 8 || drlevel < 0 || half_k > 16) {  // shuffle.cpp:26-33
+    if (half_k < half_subk || half_subk < 1 || half_subk >= 8 || drlevel < 0 || half_k > 16 || drlevel >= half_subk) {  // shuffle.cpp:26-33
         set_error("set_params: need half_subk <= half_k <= 16, 1 <= half_subk < 8 (got k=%d s=%d l=%d)", half_k, half_subk, drlevel);
         return KSSD_E_ARG;
     }
-    if (half_k - drlevel > 8) {  // sketch.cpp:336 use64
-        set_error("half_k - drlevel = %d > 8 selects the reference's 64-bit hash path, not implemented", half_k - drlevel);
-        return KSSD_E_UNSUPPORTED;
-    }
+    c->hash64 = half_k - drlevel > 8;  // sketch.cpp:336 use64: hashes of up to 4 * (half_k - drlevel) bits (hash64.cu)
     ScanParams &sp = c->sp;
     sp.half_k = half_k;
     sp.half_subk = half_subk;

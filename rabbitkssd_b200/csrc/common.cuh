@@ -114,6 +114,7 @@ struct kssd_ctx {
 
     // parameters + tables
     bool have_params = false;
+    bool relax_guard = false;  // accept half_subk - drlevel < 3 (L5K10 of BASELINE config 4: the reference refuses it, common.cpp:37-39)
     kssd::ScanParams sp;
     kssd::DevBuf d_bitmap, d_tab_keys;  // membership bitmap, exact (dim_id<<32|value) table
 
@@ -128,6 +129,7 @@ struct kssd_ctx {
     kssd::HostBuf h_snap;                  // pinned: emit cursor after the last scan of staging buffer 0 / 1
     kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
     kssd::DevBuf d_emit_rank; // u32 rank of each key inside its genome
+    kssd::DevBuf d_emit_gen;  // 64-bit hash configuration: u32 genome of each key (d_emit then holds the bare hashes)
     uint64_t emit_cap = 0;
     kssd::DevBuf d_cursor;    // u64 cursor (+ spare words)
     kssd::DevBuf d_gcount;    // u32 emitted keys per genome (written by the scan kernel)
@@ -150,7 +152,18 @@ struct kssd_ctx {
 
     // index (CSR over distinct hashes)
     bool have_index = false;
-    bool hash64 = false;       // d_uniq_hash / sketches hold 64-bit hashes (half_k - drlevel > 8, src/sketch.cpp:336)
+    // 64-bit hash configuration (half_k - drlevel > 8, src/sketch.cpp:336), hash64.cu: hashes are dictionary-encoded -- the
+    // sorted distinct hashes of a session / of an index form a dictionary and everything downstream (per-genome sort +
+    // unique, index build, counters) runs on the u32 RANKS in it, i.e. through the 32-bit kernels
+    bool hash64 = false;       // the parameters select 64-bit hashes: sketch sessions produce u64 hashes
+    int rank_bits = 0;         // bits of the ranks in the current session's dictionary (sizes the sort buckets)
+    bool index_hash64 = false; // the loaded index is over 64-bit hashes: d_uniq_hash64 holds its sorted distinct hashes
+    kssd::DevBuf d_h64_a, d_h64_b;   // scratch: u64 keys being sorted
+    kssd::DevBuf d_dict64;           // session dictionary: sorted distinct u64 hashes of all genomes of the session
+    kssd::DevBuf d_hashes64;         // finished sketch, decoded: u64 hashes (CSR with d_genome_off)
+    kssd::DevBuf d_uniq_hash64;      // index dictionary: sorted distinct u64 hashes; d_uniq_off / d_dict as in the 32-bit index
+    kssd::DevBuf d_ranks;            // index build: u32 rank of every input hash in the index dictionary
+    kssd::HostBuf h_hashes64, h_uniq_hash64;
     uint64_t n_uniq = 0, n_post = 0;
     uint32_t n_ref = 0;
     uint32_t max_ref_size = 0;
@@ -196,7 +209,14 @@ int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_ge
                   uint64_t *d_genome_off);
 // index.cu
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
-                       uint64_t total);
+                       uint64_t total, int hash_bits_override = 0);
+// hash64.cu: dictionary encoding of 64-bit hashes
+int dict_build(kssd_ctx *c, const uint64_t *d_vals, uint64_t n, int hash_bits, DevBuf &dict, uint64_t *n_dict);
+int dict_ranks(kssd_ctx *c, const uint64_t *d_vals, uint64_t n, const uint64_t *d_dict, uint64_t n_dict, uint32_t *d_ranks);
+int session_encode64(kssd_ctx *c, uint64_t n_emit, uint64_t *n_dict);   // d_emit: hash -> (genome << 32 | rank)
+int session_decode64(kssd_ctx *c, uint64_t n_keep);                     // d_hashes (ranks) -> d_hashes64
+int index_build_device64(kssd_ctx *c, const uint64_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total);
+
 int index_build_range(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total, uint32_t part,
                       uint32_t parts, uint32_t *d_block, uint64_t block_words, uint64_t *used_words, int *overflow);
 int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_words, uint32_t parts, const uint64_t *d_genome_off, uint32_t n_genomes,

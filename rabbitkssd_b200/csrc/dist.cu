@@ -484,7 +484,7 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     a.q_hashes = d_q_hashes;
     a.work = c->d_q_list_begin.as<uint2>();
     a.work_fill = c->d_q_list_end.as<uint32_t>();
-    a.uniq_hash = c->d_uniq_hash.p;
+    a.uniq_hash = c->index_hash64 ? c->d_uniq_hash64.p : c->d_uniq_hash.p;
     a.uniq_off = c->d_uniq_off.as<uint64_t>();
     a.bucket = c->d_bucket.as<uint32_t>();
     a.n_uniq = c->n_uniq;
@@ -527,7 +527,7 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
         int rc;
         if (triangle) {
             rc = wide ? launch_tiles<uint32_t, uint32_t, true>(c, a, n_tiles, smem, 1ull << 42) : launch_tiles<uint16_t, uint32_t, true>(c, a, n_tiles, smem, 1ull << 43);
-        } else if (c->hash64) {
+        } else if (c->index_hash64) {
             rc = wide ? launch_tiles<uint32_t, uint64_t, false>(c, a, n_tiles, smem, 1ull << 44) : launch_tiles<uint16_t, uint64_t, false>(c, a, n_tiles, smem, 1ull << 45);
         } else {
             rc = wide ? launch_tiles<uint32_t, uint32_t, false>(c, a, n_tiles, smem, 1ull << 46) : launch_tiles<uint16_t, uint32_t, false>(c, a, n_tiles, smem, 1ull << 47);

@@ -24,18 +24,49 @@ namespace {
 
 using kssd_host::check;
 
-// .index / .dict of the 32-bit path, as written by transSketches (sketch.cpp:1006-1011)
+// .index / .dict as written by transSketches: 32-bit path (sketch.cpp:1006-1011) { hashSize, totalIndex, count[hashSize] };
+// 64-bit path (sketch.cpp:951-958) { hash_number, hash[hash_number], count[hash_number] }, lists in the same order
 struct IndexFiles {
     size_t hashSize = 0;
     uint64_t totalIndex = 0;
+    std::vector<uint64_t> hash64;
     std::vector<uint32_t> counts, dict;
 };
 
-void read_index(const std::string &indexFile, const std::string &dictFile, const char *who, IndexFiles &ix) {
+void read_index(const std::string &indexFile, const std::string &dictFile, const char *who, bool use64, IndexFiles &ix) {
     FILE *fp = fopen(indexFile.c_str(), "rb");
     if (!fp) {
         std::cerr << "ERROR: " << who << ", cannot open the index sketch file: " << indexFile << std::endl;
         exit(1);
+    }
+    if (use64) {  // dist.cpp:38-54
+        size_t hash_number = 0;
+        const size_t r0 = fread(&hash_number, sizeof(size_t), 1, fp);
+        ix.hash64.resize(hash_number);
+        ix.counts.resize(hash_number);
+        const size_t r1 = fread(ix.hash64.data(), sizeof(uint64_t), hash_number, fp);
+        const size_t r2 = fread(ix.counts.data(), sizeof(uint32_t), hash_number, fp);
+        fclose(fp);
+        if (r0 != 1 || r1 != hash_number || r2 != hash_number) {
+            std::cerr << "ERROR: " << who << ", error read hash_number, hash_arr, and hash_size_arr" << std::endl;
+            exit(1);
+        }
+        ix.hashSize = hash_number;
+        ix.totalIndex = 0;
+        for (uint32_t n : ix.counts) ix.totalIndex += n;
+        ix.dict.resize(ix.totalIndex);
+        FILE *fd = fopen(dictFile.c_str(), "rb");
+        if (!fd) {
+            std::cerr << "ERROR: " << who << ", cannot open dict file: " << dictFile << std::endl;
+            exit(1);
+        }
+        const size_t r3 = fread(ix.dict.data(), sizeof(uint32_t), ix.totalIndex, fd);
+        fclose(fd);
+        if (r3 != ix.totalIndex) {
+            std::cerr << "ERROR: " << who << ", the read hash number is not equal to the saved hash number information" << std::endl;
+            exit(1);
+        }
+        return;
     }
     const size_t r0 = fread(&ix.hashSize, sizeof(size_t), 1, fp);
     const size_t r1 = fread(&ix.totalIndex, sizeof(uint64_t), 1, fp);
@@ -60,17 +91,39 @@ void read_index(const std::string &indexFile, const std::string &dictFile, const
     }
 }
 
-void flatten(const std::vector<sketch_t> &sk, std::vector<uint32_t> &flat, std::vector<uint64_t> &off, std::vector<uint32_t> &sizes) {
-    off.assign(sk.size() + 1, 0);
-    sizes.resize(sk.size());
+// sketches -> CSR; the hashes are hashSet (u32) or, in the 64-bit configuration, hashSet64 (sketch.h:21-22)
+struct Flat {
+    std::vector<uint32_t> h32, sizes;
+    std::vector<uint64_t> h64, off;
+};
+
+void flatten(const std::vector<sketch_t> &sk, bool use64, Flat &f) {
+    f.off.assign(sk.size() + 1, 0);
+    f.sizes.resize(sk.size());
     for (size_t i = 0; i < sk.size(); i++) {
-        sizes[i] = (uint32_t)sk[i].hashSet.size();
-        off[i + 1] = off[i] + sizes[i];
+        f.sizes[i] = (uint32_t)(use64 ? sk[i].hashSet64.size() : sk[i].hashSet.size());
+        f.off[i + 1] = f.off[i] + f.sizes[i];
     }
-    flat.resize(off.back());
-    for (size_t i = 0; i < sk.size(); i++)
-        if (sizes[i]) memcpy(flat.data() + off[i], sk[i].hashSet.data(), (size_t)sizes[i] * sizeof(uint32_t));
+    if (use64) f.h64.resize(f.off.back());
+    else f.h32.resize(f.off.back());
+    for (size_t i = 0; i < sk.size(); i++) {
+        if (!f.sizes[i]) continue;
+        if (use64) memcpy(f.h64.data() + f.off[i], sk[i].hashSet64.data(), (size_t)f.sizes[i] * sizeof(uint64_t));
+        else memcpy(f.h32.data() + f.off[i], sk[i].hashSet.data(), (size_t)f.sizes[i] * sizeof(uint32_t));
+    }
 }
+
+void load_index(kssd_ctx *ctx, bool use64, const IndexFiles &ix, const std::vector<uint32_t> &sizes) {
+    if (use64)
+        check(kssd_b200_index_load64(ctx, ix.hashSize, ix.hash64.data(), ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(),
+                                     (uint32_t)sizes.size()), "index_load64");
+    else
+        check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(), (uint32_t)sizes.size()),
+              "index_load");
+}
+
+void dist_rows(kssd_ctx *ctx, bool use64, const Flat &q, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
+               int containment, std::vector<kssd_hit> *hits);
 
 int collect_hits(void *user, const kssd_hit *hits, size_t n) {
     std::vector<kssd_hit> *v = reinterpret_cast<std::vector<kssd_hit> *>(user);
@@ -187,11 +240,15 @@ inline void for_each_cell(const std::vector<kssd_hit> &hits, size_t kb, size_t k
     }
 }
 
-void refuse64(const sketchInfo_t &info, const char *who) {
-    if (info.half_k - info.drlevel > 8) {
-        fprintf(stderr, "ERROR: %s: the 64-bit hash path is not implemented in the B200 build\n", who);
-        exit(1);
-    }
+void dist_rows(kssd_ctx *ctx, bool use64, const Flat &q, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
+               int containment, std::vector<kssd_hit> *hits) {
+    const uint32_t n = (uint32_t)q.sizes.size();
+    if (use64)
+        check(kssd_b200_dist_rows64(ctx, q.h64.data(), q.off.data(), n, KSSD_PTR_HOST, row_begin, row_end, triangle, kmer_size, max_dist,
+                                    containment, collect_hits, hits), "dist_rows64");
+    else
+        check(kssd_b200_dist_rows(ctx, q.h32.data(), q.off.data(), n, KSSD_PTR_HOST, row_begin, row_end, triangle, kmer_size, max_dist,
+                                  containment, collect_hits, hits), "dist_rows");
 }
 
 // hits sorted by (row, col); row_begin[r] .. row_begin[r+1] index the hits of row r
@@ -207,16 +264,15 @@ void group_by_row(std::vector<kssd_hit> &hits, size_t n_rows, std::vector<size_t
 void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSketchOut, string outputFile, int kmer_size,
                    double maxDist, int isContainment, int numThreads) {
     const double t0 = get_sec();
-    refuse64(info, "index_tridist()");
-    std::cerr << "-----not use hash64 in index_tridist() " << std::endl;
+    const bool use64 = info.half_k - info.drlevel > 8;  // dist.cpp:29
+    std::cerr << (use64 ? "-----use hash64 in index_tridist() " : "-----not use hash64 in index_tridist() ") << std::endl;
     IndexFiles ix;
-    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_tridist()", ix);
-    std::vector<uint32_t> flat, sizes;
-    std::vector<uint64_t> off;
-    flatten(sketches, flat, off, sizes);
+    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_tridist()", use64, ix);
+    Flat fl;
+    flatten(sketches, use64, fl);
+    const std::vector<uint32_t> &sizes = fl.sizes;
     kssd_ctx *ctx = kssd_host::context();
-    check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(), (uint32_t)sizes.size()),
-          "index_load");
+    load_index(ctx, use64, ix, sizes);
     const double t1 = get_sec();
     std::cerr << "===================time of read index and offset sketch file is: " << t1 - t0 << std::endl;
 
@@ -231,9 +287,7 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
     // (threshold +inf); the exact test below drops the ones whose distance does not pass
     const double devDist = dense ? INFINITY : maxDist;
     check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
-    check(kssd_b200_dist_rows(ctx, flat.data(), off.data(), (uint32_t)numRef, KSSD_PTR_HOST, 0, (uint32_t)numRef, 1, kmer_size, devDist,
-                              isContainment, collect_hits, &hits),
-          "dist_rows");
+    dist_rows(ctx, use64, fl, 0, (uint32_t)numRef, 1, kmer_size, devDist, isContainment, &hits);
     std::vector<size_t> row_begin;
     group_by_row(hits, numRef, row_begin);
 
@@ -271,17 +325,16 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
 void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string refSketchOut, vector<sketch_t> &query_sketches,
                 string outputFile, int kmer_size, double maxDist, uint64_t maxNeighbor, bool isNeighbor, int isContainment, int numThreads) {
     const double t0 = get_sec();
-    refuse64(ref_info, "index_dist()");
-    std::cerr << "-----not use hash64 in index_dist() " << std::endl;
+    const bool use64 = ref_info.half_k - ref_info.drlevel > 8;  // dist.cpp:435
+    std::cerr << (use64 ? "-----use hash64 in index_dist() " : "-----not use hash64 in index_dist() ") << std::endl;
     IndexFiles ix;
-    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_dist()", ix);
-    std::vector<uint32_t> rflat, rsizes, qflat, qsizes;
-    std::vector<uint64_t> roff, qoff;
-    flatten(ref_sketches, rflat, roff, rsizes);
-    flatten(query_sketches, qflat, qoff, qsizes);
+    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_dist()", use64, ix);
+    Flat rfl, qfl;
+    flatten(ref_sketches, use64, rfl);
+    flatten(query_sketches, use64, qfl);
+    const std::vector<uint32_t> &rsizes = rfl.sizes, &qsizes = qfl.sizes;
     kssd_ctx *ctx = kssd_host::context();
-    check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, rsizes.data(), (uint32_t)rsizes.size()),
-          "index_load");
+    load_index(ctx, use64, ix, rsizes);
     const double t1 = get_sec();
     std::cerr << "===================time of read the index and dict sketch file is: " << t1 - t0 << std::endl;
 
@@ -302,9 +355,7 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
     for (size_t q0 = 0; q0 < numQuery; q0 += block) {
         const size_t q1 = std::min(numQuery, q0 + block);
         std::vector<kssd_hit> hits;
-        check(kssd_b200_dist_rows(ctx, qflat.data(), qoff.data(), (uint32_t)numQuery, KSSD_PTR_HOST, (uint32_t)q0, (uint32_t)q1, 0, kmer_size,
-                                  devDist, isContainment, collect_hits, &hits),
-              "dist_rows");
+        dist_rows(ctx, use64, qfl, (uint32_t)q0, (uint32_t)q1, 0, kmer_size, devDist, isContainment, &hits);
         std::vector<size_t> row_begin;
         group_by_row(hits, numQuery, row_begin);
 #pragma omp parallel for num_threads(numThreads) schedule(static, 1)

@@ -12,7 +12,8 @@
 //  * hashSet is sorted ascending (the reference stores unordered_set iteration order, sketch.cpp:537-550);
 //  * files are not split into a "big" RabbitFX group and a "small" kseq group (sketch.cpp:352-450): every file is
 //    read with kseq; ids are still the position in the size-descending file list (sketch.cpp:365, :556).
-//  * half_k - drlevel > 8 (64-bit hashes, sketch.cpp:336) is refused with an error.
+//  * half_k - drlevel > 8 (64-bit hashes, sketch.cpp:336): hashSet64 is filled instead, sorted ascending, and the sparse
+//    .index / .dict list the hashes in ascending order (the reference writes its hash map's iteration order).
 #include <err.h>
 #include <omp.h>
 #include <sys/stat.h>
@@ -86,11 +87,7 @@ bool by_size_desc(const fileInfo_t &a, const fileInfo_t &b) { return a.fileSize 
 
 bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, const kssd_parameter_t &p, bool fastq,
                   int leastQual, int leastNumKmer, std::vector<sketch_t> &sketches, sketchInfo_t &info, std::string outputFile) {
-    if (p.half_k - p.drlevel > 8) {
-        fprintf(stderr, "ERROR: half_k - drlevel = %d > 8 needs the 64-bit hash path, which the B200 build does not implement\n",
-                p.half_k - p.drlevel);
-        exit(1);
-    }
+    const bool use64 = p.half_k - p.drlevel > 8;  // sketch.cpp:336
     // file list: as sketch.cpp:348-374 (stat every file, sort by size descending)
     std::ifstream fs(inputFile);
     if (!fs) err(errno, "cannot open the inputFile: %s\n", inputFile.c_str());
@@ -147,13 +144,15 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     filler.flush();
 
     const uint32_t *hashes = nullptr;
-    const uint64_t *off = nullptr;
-    check(kssd_b200_sketch_finish(ctx, &hashes, &off), "sketch_finish");
+    const uint64_t *hashes64 = nullptr, *off = nullptr;
+    if (use64) check(kssd_b200_sketch_finish64(ctx, &hashes64, &off), "sketch_finish64");
+    else check(kssd_b200_sketch_finish(ctx, &hashes, &off), "sketch_finish");
     for (size_t t = 0; t < n; t++) {
         sketch_t s;
         s.fileName = fileList[t].fileName;
         s.id = (int)t;
-        s.hashSet.assign(hashes + off[t], hashes + off[t + 1]);
+        if (use64) s.hashSet64.assign(hashes64 + off[t], hashes64 + off[t + 1]);
+        else s.hashSet.assign(hashes + off[t], hashes + off[t + 1]);
         sketches.push_back(s);
     }
 
@@ -186,35 +185,60 @@ bool sketchFastqFile(string inputFile, bool isQuery, int numThreads, kssd_parame
     return sketch_files(inputFile, isQuery, numThreads, parameter, true, leastQual, leastNumKmer, sketches, info, outputFile);
 }
 
-// transSketches, 32-bit path (sketch.cpp:970-1017): .dict = posting lists in ascending hash order, ids ascending
-// inside a list; .index = { size_t hashSize; uint64_t totalIndex; uint32_t count[hashSize] }.
+// transSketches (sketch.cpp:894-1021).  32-bit path (:970-1017): .dict = posting lists in ascending hash order, ids
+// ascending inside a list; .index = { size_t hashSize; uint64_t totalIndex; uint32_t count[hashSize] }.  64-bit path
+// (:904-969): .index = { size_t hash_number; uint64_t hash[hash_number]; uint32_t count[hash_number] }, .dict = the lists
+// in the same order -- the reference's order is its hash map's iteration order, here it is ascending hash.
 void transSketches(vector<sketch_t> &sketches, sketchInfo_t &info, string dictFile, string indexFile, int numThreads) {
     (void)numThreads;
-    if (info.half_k - info.drlevel > 8) {
-        fprintf(stderr, "ERROR: transSketches: the 64-bit hash path is not implemented in the B200 build\n");
-        exit(1);
+    const bool use64 = info.half_k - info.drlevel > 8;
+    std::cerr << (use64 ? "transSketches: use64" : "transSketches: not use64") << std::endl;
+    std::vector<uint64_t> off(sketches.size() + 1, 0);
+    for (size_t i = 0; i < sketches.size(); i++) off[i + 1] = off[i] + (use64 ? sketches[i].hashSet64.size() : sketches[i].hashSet.size());
+    kssd_ctx *ctx = kssd_host::context();
+    auto open_or_die = [](const std::string &path, const char *what) {
+        FILE *f = fopen(path.c_str(), "w+");
+        if (!f) {
+            std::cerr << "ERROR: transSketches, cannot open " << what << ": " << path << std::endl;
+            exit(1);
+        }
+        return f;
+    };
+    uint64_t n_uniq = 0, total = 0;
+    const uint32_t *uniq_count = nullptr, *dict = nullptr;
+    if (use64) {
+        std::vector<uint64_t> flat(off.back());
+#pragma omp parallel for schedule(dynamic, 64)
+        for (size_t i = 0; i < sketches.size(); i++)
+            if (!sketches[i].hashSet64.empty()) memcpy(flat.data() + off[i], sketches[i].hashSet64.data(), sketches[i].hashSet64.size() * sizeof(uint64_t));
+        const uint64_t *uniq_hash = nullptr;
+        check(kssd_b200_index_build64(ctx, flat.data(), off.data(), (uint32_t)sketches.size(), KSSD_PTR_HOST), "index_build64");
+        check(kssd_b200_index_export64(ctx, &n_uniq, &total, &uniq_hash, &uniq_count, &dict), "index_export64");
+        std::cerr << "the hash_number is: " << n_uniq << std::endl;
+        std::cerr << "the total size is: " << total << std::endl;
+        FILE *fp0 = open_or_die(dictFile, "dictFile");
+        fwrite(dict, sizeof(uint32_t), total, fp0);
+        fclose(fp0);
+        FILE *fp1 = open_or_die(indexFile, "indexFile");
+        const size_t hash_number = n_uniq;
+        fwrite(&hash_number, sizeof(size_t), 1, fp1);
+        fwrite(uniq_hash, sizeof(uint64_t), hash_number, fp1);
+        fwrite(uniq_count, sizeof(uint32_t), hash_number, fp1);
+        fclose(fp1);
+        return;
     }
-    std::cerr << "transSketches: not use64" << std::endl;
     const size_t hashSize = 1LLU << (4 * (info.half_k - info.drlevel));
     std::cerr << "the hashSize is: " << hashSize << std::endl;
-    std::vector<uint64_t> off(sketches.size() + 1, 0);
-    for (size_t i = 0; i < sketches.size(); i++) off[i + 1] = off[i] + sketches[i].hashSet.size();
     std::vector<uint32_t> flat(off.back());
 #pragma omp parallel for schedule(dynamic, 64)
     for (size_t i = 0; i < sketches.size(); i++)
         if (!sketches[i].hashSet.empty()) memcpy(flat.data() + off[i], sketches[i].hashSet.data(), sketches[i].hashSet.size() * sizeof(uint32_t));
 
-    kssd_ctx *ctx = kssd_host::context();
     check(kssd_b200_index_build(ctx, flat.data(), off.data(), (uint32_t)sketches.size(), KSSD_PTR_HOST), "index_build");
-    uint64_t n_uniq = 0, total = 0;
-    const uint32_t *uniq_hash = nullptr, *uniq_count = nullptr, *dict = nullptr;
+    const uint32_t *uniq_hash = nullptr;
     check(kssd_b200_index_export(ctx, &n_uniq, &total, &uniq_hash, &uniq_count, &dict), "index_export");
 
-    FILE *fp0 = fopen(dictFile.c_str(), "w+");
-    if (!fp0) {
-        std::cerr << "ERROR: transSketches, cannot open dictFile: " << dictFile << std::endl;
-        exit(1);
-    }
+    FILE *fp0 = open_or_die(dictFile, "dictFile");
     fwrite(dict, sizeof(uint32_t), total, fp0);
     fclose(fp0);
 
@@ -226,11 +250,7 @@ void transSketches(vector<sketch_t> &sketches, sketchInfo_t &info, string dictFi
         }
         counts[uniq_hash[u]] = uniq_count[u];
     }
-    FILE *fp1 = fopen(indexFile.c_str(), "w+");
-    if (!fp1) {
-        std::cerr << "ERROR: transSketches, cannot open indexFile: " << indexFile << std::endl;
-        exit(1);
-    }
+    FILE *fp1 = open_or_die(indexFile, "indexFile");
     const uint64_t totalIndex = total;
     fwrite(&hashSize, sizeof(size_t), 1, fp1);
     fwrite(&totalIndex, sizeof(uint64_t), 1, fp1);

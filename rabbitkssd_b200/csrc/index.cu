@@ -414,6 +414,7 @@ int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_word
     cudaStream_t st = c->stream;
     *overflow = 0;
     c->have_index = false;
+    c->index_hash64 = false;
     if (parts == 0 || parts > 64) { set_error("index_adopt_parts: 1..64 parts"); return KSSD_E_ARG; }
     KSSD_TRY(c->h_scalar.reserve(64 * 16 + 64));
     uint32_t *hd = c->h_scalar.as<uint32_t>();  // 4 header words per part
@@ -452,9 +453,11 @@ int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_word
     return KSSD_OK;
 }
 
-int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total) {
+int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total,
+                       int hash_bits_override) {
     cudaStream_t st = c->stream;
     c->have_index = false;
+    c->index_hash64 = false;
     c->n_ref = n_genomes;
     c->n_post = total;
     uint32_t *d_max;
@@ -463,6 +466,7 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
     int64_t known_max = -1;
     bool done = false;
     int hash_bits = c->have_params ? 4 * (c->sp.half_k - c->sp.drlevel) : 32;
+    if (hash_bits_override) hash_bits = hash_bits_override;  // 64-bit hash configuration: the "hashes" are dictionary ranks
     if (hash_bits > 32) hash_bits = 32;
     if (total && n_genomes && !c->force_radix && total < (1ull << 32)) {
         uint32_t mh = 0;

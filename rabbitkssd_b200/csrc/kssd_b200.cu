@@ -4,5 +4,6 @@
 #include "radix.cu"
 #include "segsort.cu"
 #include "index.cu"
+#include "hash64.cu"
 #include "dist.cu"
 #include "capi.cu"

@@ -243,7 +243,7 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
         while (nb < max_count && nb < 8192) nb <<= 1;
         int lg = 0;
         while ((1u << lg) < nb) lg++;
-        const int hash_bits = std::min(32, 4 * (c->sp.half_k - c->sp.drlevel));
+        const int hash_bits = c->hash64 ? c->rank_bits : std::min(32, 4 * (c->sp.half_k - c->sp.drlevel));
         shift = std::max(0, hash_bits - lg);
     }
     const size_t smem = ((size_t)key_cap + nb) * 4;

@@ -41,7 +41,8 @@ struct ScanArgs {
     uint32_t first_emit;       // k-mers ending before this byte are context only
     const uint32_t *bitmap;    // membership bitmap followed by the second-level filter (copied to shared memory)
     const unsigned long long *table;  // exact retained-subset table: (dim_id << 32 | value), ~0 = empty
-    unsigned long long *emit;  // (genome << 32 | hash)
+    unsigned long long *emit;  // (genome << 32 | hash); 64-bit hash configuration: the hash alone
+    uint32_t *emit_gen;        // 64-bit hash configuration (half_k - drlevel > 8, src/sketch.cpp:336): genome of emit[i]; else null
     const uint64_t *seg_off;   // segment table of the buffer (coordinates: byte 0 of this launch = pos_base)
     const uint32_t *seg_genome;
     uint32_t n_seg;
@@ -172,7 +173,7 @@ __device__ __forceinline__ void canonical_dim(const ScanParams &sp, uint64_t tup
 
 // Stage 2 (exact): one k-mer END position p per lane, everything re-derived from the raw bytes with the
 // reference's semantics.  Returns true and the hash when the k-mer is retained.
-__device__ __forceinline__ bool verify_kmer(const ScanArgs &a, uint32_t p, uint32_t &hash) {
+__device__ __forceinline__ bool verify_kmer(const ScanArgs &a, uint32_t p, uint64_t &hash) {
     const ScanParams &sp = a.sp;
     const int L = sp.kmer_size;
     const int start = (int)p - (L - 1);
@@ -217,7 +218,8 @@ __device__ __forceinline__ bool verify_kmer(const ScanArgs &a, uint32_t p, uint3
         for (int i = 0; i < kWindowWords; i++) QV |= nz4(__vcmpges4(qw[i], lq4)) << (4 * i);
         if ((QV & lmask) != lmask) return false;
     }
-    hash = (uint32_t)((((uni & sp.undomask0) | ((uni & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | (uint32_t)e);
+    // dr_tuple, src/sketch.cpp:518-524: up to 4 * (half_k - drlevel) bits; the 32-bit configuration keeps the low word
+    hash = (((uni & sp.undomask0) | ((uni & sp.undomask1) << (4 * sp.half_k - 4 * sp.hoc))) >> (4 * sp.drlevel)) | (uint32_t)e;
     return true;
 }
 
@@ -327,7 +329,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
         v1 = load_chunk(a.seq, off + 16, a.n_bytes);
     };
     auto stage2 = [&](int base, int n) {  // exact path for queued positions [base, base+n), append survivors to the emit buffer
-        uint32_t p = 0, hash = 0;
+        uint32_t p = 0;
+        uint64_t hash = 0;
         bool ok = false;
         if (lane < n) {
             p = ver_pos[base + lane];
@@ -347,7 +350,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
                     if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
                 }
                 genome = __ldg(a.seg_genome + lo);
-                a.emit[at] = ((unsigned long long)genome << 32) | hash;
+                if (a.emit_gen) {
+                    a.emit[at] = hash;
+                    a.emit_gen[at] = genome;
+                } else {
+                    a.emit[at] = ((unsigned long long)genome << 32) | (uint32_t)hash;
+                }
                 if (genome >= a.n_genomes) genome = 0xFFFFFFFFu;  // not a genome of this session: never dealt
             }
             // rank of the key inside its genome = running per-genome count; survivors of one warp almost always belong
@@ -590,6 +598,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.bitmap = c->d_bitmap.as<uint32_t>();
     a.table = c->d_tab_keys.as<unsigned long long>();
     a.emit = c->d_emit.as<unsigned long long>();
+    a.emit_gen = c->hash64 ? c->d_emit_gen.as<uint32_t>() : nullptr;
     a.seg_off = d_seg_off;
     a.seg_genome = d_seg_genome;
     a.n_seg = n_seg;

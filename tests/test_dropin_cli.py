@@ -172,3 +172,52 @@ def test_alldist_straight_from_genome_list(work):
     la, lb = canon("ref"), canon("new")
     assert len(la) >= 8
     assert la == lb
+
+
+def test_64bit_hash_configuration_k12(work):
+    """-k 12 -l 3: half_k - drlevel = 9 > 8 selects the 64-bit hash path (src/sketch.cpp:336): hashSet64 in .sketch, sparse
+    .index (hash -> count, in the reference's hash-map order; ascending here), alldist / dist on the 64-bit index files
+    -- each binary also READS the other's index files (same .sketch, swapped .index/.dict)."""
+    d = work["d"]
+    _run(REF, ["shuffle", "-k", "12", "-s", "6", "-l", "3", "-o", "L3K12.shuf"], d)
+    shuf = os.path.join(d, "L3K12.shuf")
+    _both(work, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "w", "-t", "4"])
+    _both(work, ["sketch", "-q", "-L", shuf, "-i", os.path.join(d, "queries.list"), "-o", "wq", "-t", "4"])
+    a = _sketch_sets(os.path.join(work["dirs"]["ref"], "w.sketch"))
+    b = _sketch_sets(os.path.join(work["dirs"]["new"], "w.sketch"))
+    assert sorted(a) == sorted(b)
+    for n in a:
+        assert a[n].dtype == np.uint64 and len(a[n]) > 20 and np.array_equal(a[n], b[n]), n
+    assert max(int(x.max()) for x in a.values()) >= 1 << 32
+
+    def mapping(tag, stem):
+        _, names, _ = formats.read_sketch(os.path.join(work["dirs"][tag], stem + ".sketch"))
+        hashes, counts, postings = formats.read_index_dict64(os.path.join(work["dirs"][tag], stem + ".sketch.index"),
+                                                             os.path.join(work["dirs"][tag], stem + ".sketch.dict"))
+        off = np.concatenate([[0], np.cumsum(counts.astype(np.int64))])
+        return {int(h): frozenset(names[g] for g in postings[off[i]:off[i + 1]]) for i, h in enumerate(hashes)}
+    assert mapping("ref", "w") == mapping("new", "w")
+    # same .sketch everywhere; the drop-in reads the REFERENCE's index files (hash-map order) and vice versa
+    rdir, ndir = work["dirs"]["ref"], work["dirs"]["new"]
+    for f in ("w.sketch", "wq.sketch"):
+        shutil.copy(os.path.join(rdir, f), os.path.join(ndir, f))
+    for ext in (".index", ".dict"):  # built for the drop-in's own genome order: stale now
+        os.remove(os.path.join(ndir, "w.sketch" + ext))
+    _run(NEW, ["alldist", "-i", "w.sketch", "-D", "0.3", "-o", "own.alldist", "-t", "3"], ndir)   # builds its own index files
+    for ext in (".index", ".dict"):
+        os.replace(os.path.join(ndir, "w.sketch" + ext), os.path.join(ndir, "mine" + ext))
+        shutil.copy(os.path.join(rdir, "w.sketch" + ext), os.path.join(ndir, "w.sketch" + ext))
+    _both(work, ["alldist", "-i", "w.sketch", "-D", "0.3", "-o", "w.alldist", "-t", "3"])
+    la = sorted(formats.parse_dist_text(os.path.join(rdir, "w.alldist")))
+    assert len(la) >= 8
+    assert la == sorted(formats.parse_dist_text(os.path.join(ndir, "w.alldist")))
+    assert la == sorted(formats.parse_dist_text(os.path.join(ndir, "own.alldist")))
+    for extra in (["-D", "0.3"], ["-N", "2"]):
+        _both(work, ["dist", "-r", "w.sketch", "-q", "wq.sketch", "-o", "w.dist", "-t", "3"] + extra)
+        lr = sorted(formats.parse_dist_text(os.path.join(rdir, "w.dist")))
+        assert len(lr) >= 4
+        assert lr == sorted(formats.parse_dist_text(os.path.join(ndir, "w.dist")))
+    for ext in (".index", ".dict"):  # the reference reads OUR index files
+        shutil.copy(os.path.join(ndir, "mine" + ext), os.path.join(rdir, "w.sketch" + ext))
+    _run(REF, ["alldist", "-i", "w.sketch", "-D", "0.3", "-o", "w2.alldist", "-t", "3"], rdir)
+    assert la == sorted(formats.parse_dist_text(os.path.join(rdir, "w2.alldist")))

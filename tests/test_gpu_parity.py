@@ -8,7 +8,7 @@ import util
 from rabbitkssd_b200 import api, synth
 
 pytestmark = pytest.mark.gpu
-CASES = sorted(c for c in util.golden_meta().keys() if not util.use64(c))  # 64-bit hash cases: refused, see below
+CASES = sorted(util.golden_meta().keys())  # includes the 64-bit hash configuration (fa_k12s6l3: half_k - drlevel = 9)
 
 
 # every test runs on both implementations of the sorts: the shared-memory segment sorts (default) and the
@@ -46,13 +46,31 @@ def test_index_and_distances_equal_reference_golden(ctx, case):
     z = util.golden_npz(case)
     names = m["names"]
     sets = [z["set_" + n] for n in names]
-    h, off = util.flatten_sets(sets)
+    wide = util.use64(case)
+    h, off = util.flatten_sets(sets, np.uint64 if wide else np.uint32)
     sizes = np.diff(off).astype(np.int64)
+    ctx.set_params(c["k"], c["s"], c["l"], util.shuffled_dim(c["k"], c["s"], c["l"]))
     ctx.index_build(h, off)
     uh, uc, dict_ = ctx.index_export()
-    assert np.array_equal(uh.astype(np.uint64), z["index_hash"])
-    assert np.array_equal(uc, z["index_count"])
-    o_dict, _, _, _ = oracle.index_build(h, off)
+    if wide:
+        # sparse .index in the iteration order of the reference's hash map (src/sketch.cpp:937-958): same MAPPING hash ->
+        # posting list; ours comes out in ascending hash order, which is what the oracle builds on the hashes' ranks
+        assert uh.dtype == np.uint64 and np.all(np.diff(uh.astype(np.float64)) > 0)
+        want, start = {}, 0
+        for hv, cnt in zip(z["index_hash"], z["index_count"]):
+            want[int(hv)] = [int(x) for x in z["dict"][start:start + cnt]]
+            start += cnt
+        got, start = {}, 0
+        for hv, cnt in zip(uh, uc):
+            got[int(hv)] = [int(x) for x in dict_[start:start + cnt]]
+            start += cnt
+        assert got == want
+        rk, roff, _ = util.compress_hashes(sets)
+        o_dict, _, _, _ = oracle.index_build(rk, roff)
+    else:
+        assert np.array_equal(uh.astype(np.uint64), z["index_hash"])
+        assert np.array_equal(uc, z["index_count"])
+        o_dict, _, _, _ = oracle.index_build(h, off)
     assert np.array_equal(dict_, o_dict)
     for tag in ["alldist", "alldist_M1", "dist", "dist_M1", "dist_D1"]:
         cont = 1 if tag.endswith("M1") else 0
@@ -372,16 +390,77 @@ def test_tandem_repeats_duplicates(ctx):
         assert np.array_equal(a.astype(np.uint64), b), g
 
 
-def test_64bit_hash_configuration_is_refused_loudly():
-    """half_k - drlevel > 8 selects the reference's 64-bit hash path (src/sketch.cpp:336), which the library does not
-    implement yet (the oracle is already pinned for it: golden case fa_k12s6l3): set_params must
-    say so instead of computing 32-bit hashes."""
+def test_64bit_hashes_equal_oracle_random(ctx):
+    """half_k - drlevel > 8 (src/sketch.cpp:336): 36- and 40-bit hashes, several genomes, N runs / lowercase, against the
+    oracle (pinned for this configuration by the golden case fa_k12s6l3); index + alldist + dist on the u64 hashes against
+    the oracle on their ranks; sparse-index round trip through index_load64 in shuffled order."""
+    for (k, s, l, length, n) in [(12, 6, 3, 900000, 5), (11, 5, 1, 30000, 4)]:
+        fam = synth.family(99 + k, n, length, 0.02, n_contigs=3)
+        genomes = [[synth.sprinkle(c, 7 + i, n_runs=3, lowercase_frac=0.02) for c in g] for i, g in enumerate(fam)]
+        want = util.oracle_sketch(k, s, l, genomes)
+        got, h, goff = _gpu_sketch(ctx, k, s, l, genomes)
+        assert h.dtype == np.uint64
+        for g, (a, b) in enumerate(zip(got, want)):
+            assert np.array_equal(a, b), (k, g)
+        assert max(int(x.max()) for x in want if len(x)) >= 1 << 32  # the case really needs more than 32 bits
+        sizes = np.diff(goff).astype(np.int64)
+        rk, roff, uniq = util.compress_hashes(want)
+        ctx.index_build(h, goff)
+        uh, uc, dict_ = ctx.index_export()
+        o_dict, o_uh, o_uc, _ = oracle.index_build(rk, roff)
+        assert np.array_equal(uh, uniq[o_uh]) and np.array_equal(uc, o_uc) and np.array_equal(dict_, o_dict)
+        for tri, D in [(True, 0.2), (False, 0.1), (False, 1.0)]:
+            hits = ctx.dist_rows(h, goff, tri, 2 * k, D)
+            hits, _, _ = api.refine_hits(hits, sizes, sizes, 2 * k, D, tri)
+            hr, hc, hm = oracle.alldist(rk, roff, 2 * k, D) if tri else oracle.dist(rk, roff, rk, roff, 2 * k, D)
+            o = np.lexsort((hits[:, 1], hits[:, 0]))
+            assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1)), (k, tri, D)
+        # the reference's files hold the lists in hash-map order: load them shuffled
+        perm = np.random.default_rng(5).permutation(len(uh))
+        starts = np.concatenate([[0], np.cumsum(uc)])
+        shuffled = np.concatenate([dict_[starts[u]:starts[u + 1]] for u in perm]) if len(perm) else dict_
+        ctx.index_load64(uh[perm], uc[perm], shuffled, sizes.astype(np.uint32))
+        hits = ctx.dist_rows(h, goff, True, 2 * k, 0.2)
+        hits, _, _ = api.refine_hits(hits, sizes, sizes, 2 * k, 0.2, True)
+        hr, hc, hm = oracle.alldist(rk, roff, 2 * k, 0.2)
+        o = np.lexsort((hits[:, 1], hits[:, 0]))
+        assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1))
+
+
+def test_hash_width_mismatch_is_refused():
     from rabbitkssd_b200 import _lib
+    import ctypes as C
     c = api.Context(0)
     try:
-        with pytest.raises(_lib.KssdError) as e:
-            c.set_params(12, 6, 3, util.shuffled_dim(12, 6, 3))
-        assert e.value.code == -3 and "64-bit" in str(e.value)
+        c.set_params(12, 6, 3, util.shuffled_dim(12, 6, 3))
+        c.sketch_begin(1)
+        hp, op = _lib.u32p(), _lib.u64p()
+        assert c.lib.kssd_b200_sketch_finish(c.h, C.byref(hp), C.byref(op)) == -2  # KSSD_E_ARG: 64-bit session, 32-bit entry point
     finally:
         c.close()
 
+
+def test_relaxed_guard_L5K10(ctx):
+    """BASELINE config 4 names L5K10 (half_subk 7, drlevel 5), which the reference refuses (common.cpp:37-39); the library
+    refuses it too unless kssd_b200_set_relax_guard is on.  Parity UNPINNED (no reference output exists): checked against
+    the oracle with the same guard relaxed.  Run here at s = 5, l = 3 (the same s - l = 2, 1 MiB table)."""
+    from rabbitkssd_b200 import _lib
+    k, s, l = 10, 5, 3
+    dim = oracle.shuffle_dim(k, s, l)
+    with pytest.raises(_lib.KssdError) as e:
+        ctx.set_params(k, s, l, dim)
+    assert e.value.code == -4
+    ctx.set_relax_guard(True)
+    try:
+        ctx.set_params(k, s, l, dim)
+        genomes = synth.family(31, 3, 400000, 0.02, n_contigs=2)
+        seq, _, off = synth.pack_batch(genomes)
+        h, goff = ctx.sketch(seq, off)
+        p = oracle.init_params(k, s, l, relax_guard=True)
+        oseq, rec_off, rec_first = synth.oracle_records(genomes)
+        want = oracle.sketch_batch(p, dim, oseq, rec_off, rec_first)
+        for g in range(3):
+            assert np.array_equal(h[int(goff[g]):int(goff[g + 1])].astype(np.uint64), want[g]), g
+        assert sum(len(x) for x in want) > 100
+    finally:
+        ctx.set_relax_guard(False)
