@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--nccl-gather", action="store_true", help="N > 1: gather the sketch shards with one NCCL all-gather instead of peer-memory reads")
     ap.add_argument("--index-sharded", action="store_true", help="N > 1: build the index sharded by hash range and all-gather the pieces")
+    ap.add_argument("--index-replicated", action="store_true", help="N > 1: every rank builds the whole index (default: the index restricted to its own row block)")
     ap.add_argument("--phases", action="store_true", help="diagnostic: per-phase wall times (synchronised) on stderr after the timed runs")
     ap.add_argument("--cpu-sample-genomes", type=int, default=256)
     ap.add_argument("--ref-batch-genomes", type=int, default=1000, help="reference arm: FASTA files on disk at a time")
@@ -278,7 +279,7 @@ def gen_genomes_device(torch, n_local, first_genome, length, family, stride):
 def run_b200(args):
     import torch
     import torch.distributed as dist
-    from rabbitkssd_b200 import api
+    from rabbitkssd_b200 import _lib, api
     from rabbitkssd_b200.multigpu import PeerGather, build_index_sharded, gather_sketches, gather_sketches_device, triangle_bounds
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -353,10 +354,22 @@ def run_b200(args):
         else:
             ph, po = d_h, d_o
         t0 = mark("gather", t0)
-        # every rank builds the whole index from the gathered sketches; the build sharded by hash range + all-gather of
-        # the pieces (--index-sharded) measured the same at 4 GPUs (profiles/r01u)
-        if world == 1 or not args.index_sharded or not build_index_sharded(dist, ctx, ph, po, n_total, state["total_all"], rank, world):
+        # N > 1: every rank indexes only what its own block of triangle rows streams (kssd_b200_index_build_rows: ~1/N of the
+        # postings).  Alternatives kept for comparison: the whole index on every rank (--index-replicated, round 1) and the
+        # build sharded by hash range + all-gather of the pieces (--index-sharded; same time as replicated at 4 GPUs, r01u)
+        rr = rows or (r0, r1)
+        if world == 1 or rr == (0, n_total) or args.index_replicated:
             ctx.index_build_device(ph, po, n_total)
+        elif args.index_sharded:
+            if not build_index_sharded(dist, ctx, ph, po, n_total, state["total_all"], rank, world):
+                ctx.index_build_device(ph, po, n_total)
+        else:
+            try:
+                ctx.index_build_rows_device(ph, po, n_total, rr)
+            except _lib.KssdError as e:
+                if e.code != -5:  # KSSD_E_OVERFLOW: a crowded bucket -> full build
+                    raise
+                ctx.index_build_device(ph, po, n_total)
         t0 = mark("index", t0)
         d_hits, n_hits = ctx.dist_rows_device(ph, po, n_total, True, 2 * K, MAX_DIST, 0, rows=rows or (r0, r1))
         t0 = mark("dist", t0)
@@ -488,12 +501,12 @@ def run_b200(args):
     e2e_lines = lines_from_hits(*api.refine_hits(all_e2e, sizes, sizes, 2 * K, MAX_DIST, True), sizes)
     parity = {"pairs_passing": len(gpu_lines), "sha256": lines_sha256(gpu_lines), "e2e_set_equal": gpu_lines == e2e_lines,
               "device_hits_superset": int(len(all_hits))}
-    if world > 1:  # the index is replicated: rank 0 can run the whole triangle alone and compare the sets
-        ctx.dist_rows_device(state["ph"], state["po"], n_total, True, 2 * K, MAX_DIST, 0, rows=(0, n_total))
+    if world > 1:  # every rank holds all sketches: rank 0 can run the whole triangle alone and compare the sets
+        ctx.index_build_device(state["ph"], state["po"], n_total)
         hp, n1 = ctx.dist_rows_device(state["ph"], state["po"], n_total, True, 2 * K, MAX_DIST, 0, rows=(0, n_total))
         one = dev_tensor(torch, hp, int(n1) * 3, torch.int32).cpu().numpy().view(np.uint32).reshape(-1, 3)
         one_lines = lines_from_hits(*api.refine_hits(one, sizes, sizes, 2 * K, MAX_DIST, True), sizes)
-        parity.update(set_equal=gpu_lines == one_lines, checked_against="the full triangle run on rank 0 alone (same index); "
+        parity.update(set_equal=gpu_lines == one_lines, checked_against="the full triangle run on rank 0 alone (full index built from the gathered sketches); "
                       "its sha256 equals the N=1 line's, which is checked against the reference binary")
 
     peak, peak_src = measured_hbm_peak()

@@ -152,6 +152,14 @@ int kssd_b200_sketch_gather_peers(kssd_ctx *ctx, const uint32_t **d_hashes, cons
 #define KSSD_PTR_DEVICE 1
 int kssd_b200_index_build(kssd_ctx *ctx, const uint32_t *hashes, const uint64_t *genome_off, uint32_t n_genomes,
                           int ptr_kind);
+/* Multi-GPU alldist (the triangle is sharded by query-row blocks; every rank needs "the index"): the index
+ * RESTRICTED to what rows [row_begin, row_end) of the triangle stream -- only the posting lists of hashes that occur in
+ * those rows' sketches (selected through a hashed bitmap: a false positive only adds a list no row of the block walks)
+ * and of these only the ids >= row_begin (src/dist.cpp:207 looks at columns > row).  Every rank then sorts ~1/ranks of
+ * the postings instead of repeating the whole build.  kssd_b200_dist_rows* accepts only triangle = 1 with rows inside
+ * the block afterwards; index_export returns the restricted lists.  KSSD_E_OVERFLOW: call kssd_b200_index_build. */
+int kssd_b200_index_build_rows(kssd_ctx *ctx, const uint32_t *hashes, const uint64_t *genome_off, uint32_t n_genomes,
+                               int ptr_kind, uint32_t row_begin, uint32_t row_end);
 int kssd_b200_index_export(kssd_ctx *ctx, uint64_t *n_uniq, uint64_t *total, const uint32_t **uniq_hash,
                            const uint32_t **uniq_count, const uint32_t **dict);
 /* 64-bit hash configuration: replaces transSketches' hash-map path (src/sketch.cpp:904-969).  index_export64 returns the

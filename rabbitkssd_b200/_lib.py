@@ -53,6 +53,7 @@ SYMBOLS = {
     "kssd_b200_sketch_publish": (C.c_int, [C.c_void_p]),
     "kssd_b200_sketch_gather_peers": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), u64p, C.POINTER(C.c_int)]),
     "kssd_b200_index_build": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]),
+    "kssd_b200_index_build_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32]),
     "kssd_b200_index_build_range": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint64,
                                               u64p, C.POINTER(C.c_int)]),
     "kssd_b200_index_adopt_parts": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_int)]),

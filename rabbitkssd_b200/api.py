@@ -214,6 +214,18 @@ class Context:
         fn = self.lib.kssd_b200_index_build64 if hash64 else self.lib.kssd_b200_index_build
         check(fn(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1))
 
+    def index_build_rows(self, hashes, genome_off, rows):
+        """Index restricted to the alldist rows [rows[0], rows[1]) (multi-GPU row sharding)."""
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint32)
+        genome_off = np.ascontiguousarray(genome_off, dtype=np.uint64)
+        self.index64 = False
+        check(self.lib.kssd_b200_index_build_rows(self.h, C.c_void_p(hashes.ctypes.data), C.c_void_p(genome_off.ctypes.data),
+                                                  len(genome_off) - 1, 0, rows[0], rows[1]))
+
+    def index_build_rows_device(self, d_hashes, d_genome_off, n_genomes, rows):
+        self.index64 = False
+        check(self.lib.kssd_b200_index_build_rows(self.h, C.c_void_p(d_hashes), C.c_void_p(d_genome_off), n_genomes, 1, rows[0], rows[1]))
+
     def index_build_range(self, d_hashes, d_genome_off, n_genomes, part, parts, d_block, block_words):
         """CSR of hash range `part` of `parts` packed into the caller's device block -> (overflow flag, words used)."""
         ov, used = C.c_int(), C.c_uint64()

@@ -165,6 +165,9 @@ struct kssd_ctx {
     kssd::DevBuf d_ranks;            // index build: u32 rank of every input hash in the index dictionary
     kssd::HostBuf h_hashes64, h_uniq_hash64;
     uint64_t n_uniq = 0, n_post = 0;
+    uint64_t list_slots = 0;   // hashes of all indexed sketches: bounds the alldist work lists (a row has <= |sketch| ranges)
+    uint32_t index_row_begin = 0, index_row_end = 0xFFFFFFFFu;  // index restricted to these alldist rows (index_build_rows)
+    kssd::DevBuf d_filter;     // index_build_rows: hashed bitmap of the hashes of the row block
     uint32_t n_ref = 0;
     uint32_t max_ref_size = 0;
     kssd::DevBuf d_uniq_hash, d_uniq_off, d_dict, d_ref_sizes, d_pairs, d_pairs_tmp;
@@ -209,7 +212,7 @@ int split_genomes(kssd_ctx *c, const uint64_t *d_keys, uint64_t n, uint32_t n_ge
                   uint64_t *d_genome_off);
 // index.cu
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes,
-                       uint64_t total, int hash_bits_override = 0);
+                       uint64_t total, int hash_bits_override = 0, uint32_t row_begin = 0, uint32_t row_end = 0xFFFFFFFFu);
 // hash64.cu: dictionary encoding of 64-bit hashes
 int dict_build(kssd_ctx *c, const uint64_t *d_vals, uint64_t n, int hash_bits, DevBuf &dict, uint64_t *n_dict);
 int dict_ranks(kssd_ctx *c, const uint64_t *d_vals, uint64_t n, const uint64_t *d_dict, uint64_t n_dict, uint32_t *d_ranks);

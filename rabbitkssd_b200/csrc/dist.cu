@@ -432,6 +432,10 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
         set_error("dist: triangle (alldist) needs the indexed sketches as queries (%u queries, %u indexed)", n_query, c->n_ref);
         return KSSD_E_ARG;
     }
+    if (c->index_row_end != 0xFFFFFFFFu && (!triangle || row_begin < c->index_row_begin || row_end > c->index_row_end)) {
+        set_error("dist: the index was built for alldist rows [%u, %u) only (index_build_rows)", c->index_row_begin, c->index_row_end);
+        return KSSD_E_ARG;
+    }
     if (row_begin == row_end || c->n_ref == 0) return KSSD_OK;
     cudaStream_t st = c->stream;
     const uint32_t rows = row_end - row_begin;
@@ -445,8 +449,8 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     KSSD_CUDA(cudaMemsetAsync(d_cursor, 0, 24, st));
     if (c->profiling) KSSD_TRY(c->t_count.begin(st));
     if (triangle) {
-        // posting ranges per row; slots of row g start at q_off[g] (<= n_post in total: queries are the indexed sketches)
-        KSSD_TRY(c->d_q_list_begin.reserve(std::max<uint64_t>(c->n_post, 1) * sizeof(uint2), st));
+        // posting ranges per row; slots of row g start at q_off[g] (<= list_slots in total: queries are the indexed sketches)
+        KSSD_TRY(c->d_q_list_begin.reserve(std::max<uint64_t>(c->list_slots, 1) * sizeof(uint2), st));
         KSSD_TRY(c->d_q_list_end.reserve((uint64_t)rows * 4, st));
         KSSD_CUDA(cudaMemsetAsync(c->d_q_list_end.p, 0, (uint64_t)rows * 4, st));
         if (c->n_uniq) {

@@ -140,28 +140,61 @@ static constexpr uint32_t kBucketCapSmall = 3072, kBucketCapLarge = 8192;  // pa
 #endif
 static constexpr uint32_t kSubBuckets = KSSD_SUB_BUCKETS;                               // counting-sort buckets inside a bucket
 
-// Both passes can be restricted to the hashes in [h_lo, h_last] (multi-GPU: every rank builds the CSR of one hash range,
-// index_build_range); buckets are then relative to h_lo.
-__global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, uint64_t total, int shift, uint32_t last_bucket,
-                                                          uint32_t h_lo, uint32_t h_last, uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const uint32_t h = hashes[i];
-    if (h < h_lo || h > h_last) return;
-    rank[i] = atomicAdd(bcount + min((h - h_lo) >> shift, last_bucket), 1u);  // arrival order inside the bucket
+// Both passes can be restricted (a) to the hashes in [h_lo, h_last] (multi-GPU: every rank builds the CSR of one hash
+// range, index_build_range; buckets are then relative to h_lo) and (b) to the postings a block of alldist rows needs
+// (index_build_rows): genomes >= g_begin only, and only hashes whose bit is set in `filter`, a hashed bitmap of the hashes
+// that occur in the rows of the block (false positives only add lists that no row of the block streams).
+struct PostingFilter {
+    const uint32_t *bits;  // null: no filter
+    uint32_t mask;         // bitmap size in bits - 1
+    uint32_t g_begin;      // postings of genomes below this are dropped
+};
+__device__ __forceinline__ uint32_t filter_slot(uint32_t h, uint32_t mask) { return (h * 0x9E3779B1u) >> 3 & mask; }
+__device__ __forceinline__ bool filter_pass(const PostingFilter &f, uint32_t h) {
+    if (!f.bits) return true;
+    const uint32_t s = filter_slot(h, f.mask);
+    return (__ldg(f.bits + (s >> 5)) >> (s & 31)) & 1u;
 }
 
-// grid = (genomes, chunks): the genome id is blockIdx.x; the slot inside the bucket was drawn by the histogram pass
-__global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
-                                                          uint32_t last_bucket, uint32_t h_lo, uint32_t h_last, const uint64_t *__restrict__ bstart,
-                                                          const uint32_t *__restrict__ rank, uint64_t *__restrict__ pairs) {
+// rows [row_begin, row_end) -> filter bits
+__global__ void __launch_bounds__(256) filter_set_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, uint32_t row_begin,
+                                                         uint32_t row_end, uint32_t mask, uint32_t *__restrict__ bits) {
+    const uint64_t e0 = genome_off[row_begin], e1 = genome_off[row_end];
+    for (uint64_t e = e0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t s = filter_slot(hashes[e], mask);
+        atomicOr(bits + (s >> 5), 1u << (s & 31));
+    }
+}
+
+// grid = (genomes, chunks): the genome id is blockIdx.x.  Counts the pairs per bucket and draws each pair's arrival rank
+// inside its bucket (0xFFFFFFFF: the pair is not indexed).
+__global__ void __launch_bounds__(128) bucket_hist_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
+                                                          uint32_t last_bucket, uint32_t h_lo, uint32_t h_last, const PostingFilter f,
+                                                          uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
     const uint32_t g = blockIdx.x;
+    if (g < f.g_begin) return;
     const uint64_t e1 = genome_off[g + 1];
     for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
         const uint32_t h = hashes[e];
-        if (h < h_lo || h > h_last) continue;
+        uint32_t r = 0xFFFFFFFFu;
+        if (h >= h_lo && h <= h_last && filter_pass(f, h)) r = atomicAdd(bcount + min((h - h_lo) >> shift, last_bucket), 1u);  // arrival order
+        rank[e] = r;
+    }
+}
+
+// the slot inside the bucket was drawn by the histogram pass
+__global__ void __launch_bounds__(128) bucket_deal_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
+                                                          uint32_t last_bucket, uint32_t h_lo, uint32_t g_begin, const uint64_t *__restrict__ bstart,
+                                                          const uint32_t *__restrict__ rank, uint64_t *__restrict__ pairs) {
+    const uint32_t g = blockIdx.x;
+    if (g < g_begin) return;
+    const uint64_t e1 = genome_off[g + 1];
+    for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
+        const uint32_t r = rank[e];
+        if (r == 0xFFFFFFFFu) continue;
+        const uint32_t h = hashes[e];
         const uint32_t b = min((h - h_lo) >> shift, last_bucket);
-        pairs[bstart[b] + rank[e]] = ((uint64_t)h << 32) | g;
+        pairs[bstart[b] + r] = ((uint64_t)h << 32) | g;
     }
 }
 
@@ -244,7 +277,7 @@ __global__ void segment_scan_kernel(const uint32_t *counts, uint32_t n, uint64_t
 // buckets are cut from; expect = postings expected in the range (sizes the buckets); *n_post = postings found.
 static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total,
                                 uint32_t h_lo, uint32_t h_last, int range_bits, uint64_t expect, uint32_t *d_max_size, bool *done,
-                                uint64_t *n_uniq, uint64_t *n_post, uint32_t *max_hash) {
+                                uint64_t *n_uniq, uint64_t *n_post, uint32_t *max_hash, PostingFilter filter = PostingFilter{nullptr, 0, 0}) {
     cudaStream_t st = c->stream;
     *done = false;
     int B = 0;
@@ -263,10 +296,10 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     uint32_t *tmp_rel = tmp_hash + total;
     const uint64_t avg_len = total / n_genomes + 1;
     const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);
-    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, total, shift, nb - 1, h_lo, h_last, bcount,
-                                                                       tmp_hash /* rank, dead before the sort */);
+    bucket_hist_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, h_last, filter, bcount,
+                                                                tmp_hash /* rank, dead before the sort */);
     segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
-    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, h_last, bstart, tmp_hash,
+    bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, filter.g_begin, bstart, tmp_hash,
                                                                 c->d_pairs.as<uint64_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
@@ -447,6 +480,9 @@ int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_word
     c->max_ref_size = *c->h_scalar.as<uint32_t>();
     c->n_ref = n_genomes;
     c->n_post = P;
+    c->list_slots = P;
+    c->index_row_begin = 0;
+    c->index_row_end = 0xFFFFFFFFu;
     c->n_uniq = U;
     KSSD_TRY(index_build_buckets(c, U ? (int64_t)mh : -1));
     c->have_index = true;
@@ -454,12 +490,16 @@ int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_word
 }
 
 int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_genome_off, uint32_t n_genomes, uint64_t total,
-                       int hash_bits_override) {
+                       int hash_bits_override, uint32_t row_begin, uint32_t row_end) {
     cudaStream_t st = c->stream;
     c->have_index = false;
     c->index_hash64 = false;
     c->n_ref = n_genomes;
     c->n_post = total;
+    c->list_slots = total;
+    const bool restricted = row_end != 0xFFFFFFFFu && !(row_begin == 0 && row_end >= n_genomes);
+    c->index_row_begin = restricted ? row_begin : 0;
+    c->index_row_end = restricted ? row_end : 0xFFFFFFFFu;
     uint32_t *d_max;
     KSSD_TRY(index_scratch(c, n_genomes, total, d_genome_off, &d_max));
     uint64_t n_uniq = 0;
@@ -468,7 +508,33 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
     int hash_bits = c->have_params ? 4 * (c->sp.half_k - c->sp.drlevel) : 32;
     if (hash_bits_override) hash_bits = hash_bits_override;  // 64-bit hash configuration: the "hashes" are dictionary ranks
     if (hash_bits > 32) hash_bits = 32;
-    if (total && n_genomes && !c->force_radix && total < (1ull << 32)) {
+    if (restricted) {
+        // alldist rows [row_begin, row_end) only (multi-GPU row sharding): a row streams the lists of ITS hashes,
+        // and of those only the ids above itself (src/dist.cpp:207) -- index just those postings.  Work ~ 1/ranks of the full
+        // build, which every rank would otherwise repeat.
+        if (row_begin >= row_end || row_end > n_genomes) { set_error("index_build_rows: bad row range"); return KSSD_E_ARG; }
+        if (c->force_radix || total >= (1ull << 32)) { set_error("index_build_rows: needs the bucketed build (< 2^32 postings)"); return KSSD_E_UNSUPPORTED; }
+        PostingFilter f;
+        f.mask = (1u << 27) - 1;  // 16 MB hashed bitmap: L2 resident; ~1 % false positives at 1.5 M hashes
+        f.g_begin = row_begin;
+        KSSD_TRY(c->d_filter.reserve(((uint64_t)f.mask + 1) / 8, st));
+        f.bits = c->d_filter.as<uint32_t>();
+        KSSD_CUDA(cudaMemsetAsync(c->d_filter.p, 0, ((uint64_t)f.mask + 1) / 8, st));
+        const uint64_t own = total / n_genomes * (row_end - row_begin) + 1;  // ~ hashes in the rows of the block
+        filter_set_kernel<<<(unsigned)std::min<uint64_t>((own + 255) / 256, (uint64_t)c->sm_count * 8), 256, 0, st>>>(d_hashes, d_genome_off, row_begin, row_end,
+                                                                                                              f.mask, c->d_filter.as<uint32_t>());
+        KSSD_CUDA(cudaGetLastError());
+        c->launches++;
+        uint32_t mh = 0;
+        uint64_t n_post = 0;
+        if (total) KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, 0u, 0xFFFFFFFFu, hash_bits, 2 * own + 1024, d_max, &done, &n_uniq, &n_post, &mh, f));
+        if (!done && total) {  // a crowded bucket (the estimate of the passing postings was far off): callers build the full index
+            set_error("index_build_rows: bucket overflow");
+            return KSSD_E_OVERFLOW;
+        }
+        known_max = mh;
+        c->n_post = n_post;
+    } else if (total && n_genomes && !c->force_radix && total < (1ull << 32)) {
         uint32_t mh = 0;
         uint64_t n_post = 0;
         KSSD_TRY(index_build_bucketed(c, d_hashes, d_genome_off, n_genomes, total, 0u, 0xFFFFFFFFu, hash_bits, total, d_max, &done, &n_uniq, &n_post, &mh));

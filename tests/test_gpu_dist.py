@@ -177,3 +177,39 @@ def test_peer_gather_across_processes(world):
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, f"rank {r}:\n{o[-3000:]}"
         assert "PEER_OK" in o, f"rank {r}:\n{o[-3000:]}"
+
+
+def test_row_restricted_index_equals_full_index():
+    """kssd_b200_index_build_rows: for every block of alldist rows the restricted index must give exactly the hits of the
+    full index for those rows, and hold fewer postings; rows outside the block and dist (rectangle) are refused."""
+    from rabbitkssd_b200 import _lib
+    h, off = synth.synth_sketches(991, 60, 8, 300, 28)
+    n = len(off) - 1
+    c = api.Context(0)
+    try:
+        c.set_params(10, 6, 3, util.shuffled_dim(10, 6, 3))
+        c.index_build(h, off)
+        full = c.dist_rows(h, off, True, 20, 0.1)
+        full = full[np.lexsort((full[:, 1], full[:, 0]))]
+        _, _, full_dict = c.index_export()
+        assert len(full) > 500
+        parts = []
+        for (r0, r1) in [(0, 100), (100, 101), (101, 333), (333, n)]:
+            c.index_build_rows(h, off, (r0, r1))
+            _, _, d = c.index_export()
+            assert len(d) < len(full_dict) and (r0 == 0 or d.min() >= r0)
+            got = c.dist_rows(h, off, True, 20, 0.1, rows=(r0, r1))
+            parts.append(got)
+            with pytest.raises(_lib.KssdError):
+                c.dist_rows(h, off, False, 20, 0.1, rows=(r0, r1))
+            if r0 > 0:
+                with pytest.raises(_lib.KssdError):
+                    c.dist_rows(h, off, True, 20, 0.1, rows=(r0 - 1, r1))
+        got = np.concatenate(parts)
+        got = got[np.lexsort((got[:, 1], got[:, 0]))]
+        assert np.array_equal(got, full)
+        c.index_build_rows(h, off, (0, n))  # the whole triangle: a plain full build again
+        _, _, d = c.index_export()
+        assert np.array_equal(d, full_dict)
+    finally:
+        c.close()
