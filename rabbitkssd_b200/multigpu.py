@@ -159,3 +159,32 @@ def gather_sketches(dist, hashes_local, sizes_local, world):
     off = torch.zeros(world * n_local + 1, dtype=torch.int64, device=dev)
     off[1:] = torch.cumsum(sizes_all, 0)
     return hashes, off
+
+
+def replicate_index(dist, ctx, rank, root=0):
+    """The reference index replicated by NCCL broadcast over NVLink (north_star): the root's CSR (distinct
+    hashes, list starts, postings, reference sizes: kssd_b200_index_device_views) is broadcast array by array and adopted
+    by every other rank's context (kssd_b200_index_adopt_device)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    v = ctx.index_device_views() if rank == root else None
+    shape = torch.tensor([v["n_uniq"], v["total"], v["n_ref"]] if v else [0, 0, 0], dtype=torch.int64, device=dev)
+    dist.broadcast(shape, root)
+    n_uniq, total, n_ref = (int(x) for x in shape.tolist())
+
+    def view(ptr, n, dtype, ts):
+        class V:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": ts, "data": (ptr, False), "version": 2}
+        return torch.as_tensor(V(), device=dev) if n else torch.zeros(0, dtype=dtype, device=dev)
+    spec = [("d_uniq_hash", n_uniq, torch.int32, "<i4"), ("d_uniq_off", n_uniq + 1, torch.int64, "<i8"),
+            ("d_dict", total, torch.int32, "<i4"), ("d_ref_sizes", n_ref, torch.int32, "<i4")]
+    bufs = {}
+    for name, n, dtype, ts in spec:
+        t = view(v[name], n, dtype, ts).clone() if rank == root else torch.empty(n, dtype=dtype, device=dev)
+        if n:
+            dist.broadcast(t, root)
+        bufs[name] = t
+    if rank != root:
+        torch.cuda.current_stream().synchronize()
+        ctx.index_adopt_device(n_uniq, total, n_ref, bufs["d_uniq_hash"].data_ptr(), bufs["d_uniq_off"].data_ptr(),
+                               bufs["d_dict"].data_ptr(), bufs["d_ref_sizes"].data_ptr())
+    return n_uniq, total, n_ref
