@@ -41,6 +41,9 @@ int kssd_b200_version(void);
  * the GPU path (kssd_b200_set_params); generating it stays on the CPU as in the reference. */
 int kssd_b200_shuffle_table(int half_k, int half_subk, int drlevel, int32_t *out);
 
+/* Number of usable CUDA devices (0 and KSSD_E_CUDA when there is none): a host with one context per GPU (dist_gpu.cpp)
+ * sizes its pool with it. */
+int kssd_b200_device_count(int *n);
 /* Create a context on CUDA device `device`.  Fails (KSSD_E_CUDA) when no device is usable. */
 int kssd_b200_init(kssd_ctx **ctx, int device);
 void kssd_b200_destroy(kssd_ctx *ctx);
@@ -226,6 +229,12 @@ int kssd_b200_set_emit_zero_cells(kssd_ctx *ctx, int on);
  * in when a row has fewer than max_neighbor reported cells and the threshold lets distance 1.0 pass.  0 = off (default). */
 int kssd_b200_set_max_neighbor(kssd_ctx *ctx, uint64_t max_neighbor);
 typedef int (*kssd_sink)(void *user, const kssd_hit *hits, size_t n);
+/* Query sketches to device memory ONCE, for callers that walk the rows in several dist_rows calls (a host thread per GPU
+ * streaming row blocks to its result files, dist_gpu.cpp): returns library-owned device arrays to pass with
+ * KSSD_PTR_DEVICE, valid until the next queries_upload / host-pointer dist_rows / index_build from host pointers.
+ * hash_bytes = 4 (uint32 hashes) or 8 (64-bit configuration). */
+int kssd_b200_queries_upload(kssd_ctx *ctx, const void *q_hashes, const uint64_t *q_off, uint32_t n_query, int hash_bytes,
+                             const void **d_q_hashes, const uint64_t **d_q_off);
 int kssd_b200_dist_rows(kssd_ctx *ctx, const uint32_t *q_hashes, const uint64_t *q_off, uint32_t n_query,
                         int ptr_kind, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size,
                         double max_dist, int containment, kssd_sink sink, void *user);

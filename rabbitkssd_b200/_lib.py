@@ -30,6 +30,7 @@ SYMBOLS = {
     "kssd_b200_last_error": (C.c_char_p, []),
     "kssd_b200_version": (C.c_int, []),
     "kssd_b200_shuffle_table": (C.c_int, [C.c_int, C.c_int, C.c_int, i32p]),
+    "kssd_b200_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "kssd_b200_init": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "kssd_b200_destroy": (None, [C.c_void_p]),
     "kssd_b200_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -65,6 +66,8 @@ SYMBOLS = {
                                                C.c_void_p, C.c_void_p]),
     "kssd_b200_set_emit_zero_cells": (C.c_int, [C.c_void_p, C.c_int]),
     "kssd_b200_set_max_neighbor": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "kssd_b200_queries_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.POINTER(C.c_void_p),
+                                           C.POINTER(C.c_void_p)]),
     "kssd_b200_dist_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32,
                                       C.c_int, C.c_int, C.c_double, C.c_int, SINK, C.c_void_p]),
     "kssd_b200_dist_rows_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,

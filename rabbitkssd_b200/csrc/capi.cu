@@ -118,6 +118,19 @@ int kssd_b200_shuffle_table(int half_k, int half_subk, int drlevel, int32_t *out
     return KSSD_OK;
 }
 
+int kssd_b200_device_count(int *n) {
+    if (!n) { set_error("device_count: null out pointer"); return KSSD_E_ARG; }
+    *n = 0;
+    int k = 0;
+    cudaError_t e = cudaGetDeviceCount(&k);
+    if (e != cudaSuccess || k == 0) {
+        set_error("no usable CUDA device (%s); libkssd_b200 has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+        return KSSD_E_CUDA;
+    }
+    *n = k;
+    return KSSD_OK;
+}
+
 int kssd_b200_init(kssd_ctx **out, int device) {
     if (!out) { set_error("null out pointer"); return KSSD_E_ARG; }
     *out = nullptr;

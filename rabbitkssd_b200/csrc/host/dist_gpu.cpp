@@ -113,18 +113,6 @@ void flatten(const std::vector<sketch_t> &sk, bool use64, Flat &f) {
     }
 }
 
-void load_index(kssd_ctx *ctx, bool use64, const IndexFiles &ix, const std::vector<uint32_t> &sizes) {
-    if (use64)
-        check(kssd_b200_index_load64(ctx, ix.hashSize, ix.hash64.data(), ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(),
-                                     (uint32_t)sizes.size()), "index_load64");
-    else
-        check(kssd_b200_index_load(ctx, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(), (uint32_t)sizes.size()),
-              "index_load");
-}
-
-void dist_rows(kssd_ctx *ctx, bool use64, const Flat &q, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
-               int containment, std::vector<kssd_hit> *hits);
-
 int collect_hits(void *user, const kssd_hit *hits, size_t n) {
     std::vector<kssd_hit> *v = reinterpret_cast<std::vector<kssd_hit> *>(user);
     v->insert(v->end(), hits, hits + n);
@@ -177,7 +165,8 @@ struct SubFiles {
             fclose(fpIndexArr[i]);
         }
         uint64_t totalSize = 0;
-        const uint64_t maxSize = 1LLU << 32;  // max total distance file size 4GB
+        uint64_t maxSize = 1LLU << 32;  // max total distance file size 4GB (dist.cpp:277)
+        if (const char *lim = getenv("KSSD_B200_MERGE_LIMIT")) maxSize = strtoull(lim, nullptr, 10);  // tests: take the split branch without 4 GiB of text
         for (int i = 0; i < numThreads; i++) {
             struct stat st;
             st.st_size = 0;
@@ -240,23 +229,102 @@ inline void for_each_cell(const std::vector<kssd_hit> &hits, size_t kb, size_t k
     }
 }
 
-void dist_rows(kssd_ctx *ctx, bool use64, const Flat &q, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,
-               int containment, std::vector<kssd_hit> *hits) {
-    const uint32_t n = (uint32_t)q.sizes.size();
-    if (use64)
-        check(kssd_b200_dist_rows64(ctx, q.h64.data(), q.off.data(), n, KSSD_PTR_HOST, row_begin, row_end, triangle, kmer_size, max_dist,
-                                    containment, collect_hits, hits), "dist_rows64");
-    else
-        check(kssd_b200_dist_rows(ctx, q.h32.data(), q.off.data(), n, KSSD_PTR_HOST, row_begin, row_end, triangle, kmer_size, max_dist,
-                                  containment, collect_hits, hits), "dist_rows");
+// One context per GPU, every one holding the reference index (query rows are sharded, the index is
+// replicated), and the query sketches uploaded once per GPU.
+struct GpuPool {
+    std::vector<kssd_ctx *> ctx;
+    std::vector<const void *> d_qh;
+    std::vector<const uint64_t *> d_qo;
+    bool use64 = false;
+    uint32_t n_query = 0;
+
+    // index: what transSketches left on device 0 when it wrote exactly these files in this process (kssd_host::index_cache),
+    // else the files (src/dist.cpp:83-130, :488-523).  Other GPUs: device 0's CSR copied over (32-bit hashes) or loaded
+    // from the host arrays too.
+    void setup(size_t want, bool use64_, const std::string &refSketchOut, const char *who, const std::vector<uint32_t> &ref_sizes, const Flat &queries) {
+        use64 = use64_;
+        n_query = (uint32_t)queries.sizes.size();
+        const std::string indexFile = refSketchOut + ".index", dictFile = refSketchOut + ".dict";
+        kssd_host::IndexCache &cache = kssd_host::index_cache();
+        const bool cached = cache.valid && cache.use64 == use64 && cache.index_file == indexFile && cache.dict_file == dictFile &&
+                            cache.n_genomes == ref_sizes.size();
+        const size_t G = std::max<size_t>(1, std::min(want, kssd_host::device_count()));
+        ctx.resize(G);
+        for (size_t g = 0; g < G; g++) ctx[g] = kssd_host::context_at(g);
+        IndexFiles ix;
+        if (cached) {
+            std::cerr << "-----" << who << ": the index built by transSketches is still on the device, " << indexFile << " is not read back" << std::endl;
+        } else {
+            kssd_host::pending_writes().wait(&indexFile);
+            read_index(indexFile, dictFile, who, use64, ix);
+            load(ctx[0], ix, ref_sizes);
+            cache = kssd_host::IndexCache{true, use64, indexFile, dictFile, ref_sizes.size()};
+        }
+        if (G > 1) {
+            if (use64 && cached) {  // no device-to-device path for the 64-bit dictionary: the other GPUs read the files
+                kssd_host::pending_writes().wait(&indexFile);
+                read_index(indexFile, dictFile, who, use64, ix);
+            }
+            uint64_t n_uniq = 0, total = 0;
+            uint32_t n_ref = 0;
+            const uint32_t *d_uh = nullptr, *d_dict = nullptr, *d_rs = nullptr;
+            const uint64_t *d_uo = nullptr;
+            if (!use64) check(kssd_b200_index_device_views(ctx[0], &n_uniq, &total, &n_ref, &d_uh, &d_uo, &d_dict, &d_rs), "index_device_views");
+#pragma omp parallel for num_threads((int)(G - 1)) schedule(static, 1)
+            for (size_t g = 1; g < G; g++) {
+                if (use64) load(ctx[g], ix, ref_sizes);
+                else check(kssd_b200_index_adopt_device(ctx[g], n_uniq, total, n_ref, d_uh, d_uo, d_dict, d_rs), "index_adopt_device");
+            }
+        }
+        d_qh.assign(G, nullptr);
+        d_qo.assign(G, nullptr);
+#pragma omp parallel for num_threads((int)G) schedule(static, 1)
+        for (size_t g = 0; g < G; g++) {
+            check(kssd_b200_set_emit_zero_cells(ctx[g], 0), "set_emit_zero_cells");
+            check(kssd_b200_queries_upload(ctx[g], use64 ? (const void *)queries.h64.data() : (const void *)queries.h32.data(), queries.off.data(), n_query,
+                                           use64 ? 8 : 4, &d_qh[g], &d_qo[g]), "queries_upload");
+        }
+    }
+
+    void load(kssd_ctx *c, const IndexFiles &ix, const std::vector<uint32_t> &sizes) {
+        if (use64)
+            check(kssd_b200_index_load64(c, ix.hashSize, ix.hash64.data(), ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(),
+                                         (uint32_t)sizes.size()), "index_load64");
+        else
+            check(kssd_b200_index_load(c, ix.hashSize, ix.counts.data(), ix.dict.data(), ix.totalIndex, sizes.data(), (uint32_t)sizes.size()),
+                  "index_load");
+    }
+
+    void rows(size_t g, uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist, int containment,
+              std::vector<kssd_hit> *hits) const {
+        if (use64)
+            check(kssd_b200_dist_rows64(ctx[g], (const uint64_t *)d_qh[g], d_qo[g], n_query, KSSD_PTR_DEVICE, row_begin, row_end, triangle, kmer_size,
+                                        max_dist, containment, collect_hits, hits), "dist_rows64");
+        else
+            check(kssd_b200_dist_rows(ctx[g], (const uint32_t *)d_qh[g], d_qo[g], n_query, KSSD_PTR_DEVICE, row_begin, row_end, triangle, kmer_size,
+                                      max_dist, containment, collect_hits, hits), "dist_rows");
+    }
+};
+
+// hits of the rows [r0, r1) sorted by (row, col); row_begin[r - r0] .. row_begin[r - r0 + 1] index the hits of row r
+void group_by_row(std::vector<kssd_hit> &hits, size_t r0, size_t r1, std::vector<size_t> &row_begin) {
+    std::sort(hits.begin(), hits.end(), [](const kssd_hit &a, const kssd_hit &b) { return a.row != b.row ? a.row < b.row : a.col < b.col; });
+    row_begin.assign(r1 - r0 + 1, 0);
+    for (const kssd_hit &h : hits) row_begin[h.row - r0 + 1]++;
+    for (size_t r = 0; r < r1 - r0; r++) row_begin[r + 1] += row_begin[r];
 }
 
-// hits sorted by (row, col); row_begin[r] .. row_begin[r+1] index the hits of row r
-void group_by_row(std::vector<kssd_hit> &hits, size_t n_rows, std::vector<size_t> &row_begin) {
-    std::sort(hits.begin(), hits.end(), [](const kssd_hit &a, const kssd_hit &b) { return a.row != b.row ? a.row < b.row : a.col < b.col; });
-    row_begin.assign(n_rows + 1, 0);
-    for (const kssd_hit &h : hits) row_begin[h.row + 1]++;
-    for (size_t r = 0; r < n_rows; r++) row_begin[r + 1] += row_begin[r];
+// another GPU is brought in (context, copy of the index) only when it gets at least this many query rows
+inline size_t min_rows_per_gpu(size_t dflt) {
+    const char *e = getenv("KSSD_B200_MIN_ROWS_PER_GPU");
+    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : dflt;
+    return v ? v : 1;
+}
+
+// GPU g of G owns the sub-files [first, first + count) of the numThreads the reference would write
+inline void files_of_gpu(size_t g, size_t G, int numThreads, int &first, int &count) {
+    first = (int)(g * (size_t)numThreads / G);
+    count = (int)((g + 1) * (size_t)numThreads / G) - first;
 }
 
 }  // namespace
@@ -266,56 +334,63 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
     const double t0 = get_sec();
     const bool use64 = info.half_k - info.drlevel > 8;  // dist.cpp:29
     std::cerr << (use64 ? "-----use hash64 in index_tridist() " : "-----not use hash64 in index_tridist() ") << std::endl;
-    IndexFiles ix;
-    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_tridist()", use64, ix);
+    if (numThreads < 1) numThreads = 1;
+    const size_t numRef = sketches.size();
     Flat fl;
     flatten(sketches, use64, fl);
     const std::vector<uint32_t> &sizes = fl.sizes;
-    kssd_ctx *ctx = kssd_host::context();
-    load_index(ctx, use64, ix, sizes);
+    GpuPool pool;
+    pool.setup(std::min<size_t>((size_t)numThreads, std::max<size_t>(1, numRef / min_rows_per_gpu(64))), use64, refSketchOut, "index_tridist()", sizes, fl);
+    const size_t G = pool.ctx.size();
     const double t1 = get_sec();
     std::cerr << "===================time of read index and offset sketch file is: " << t1 - t0 << std::endl;
 
-    const size_t numRef = sketches.size();
-    if (numThreads < 1) numThreads = 1;
     SubFiles sub(outputFile, numThreads);
     std::cerr << "=====total: " << numRef << std::endl;
-    std::vector<kssd_hit> hits;
-    check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
     const bool dense = 1.0 < maxDist;  // zero cells pass `mashD < maxDist` (dist.cpp:227-232)
     // dense: every unreported cell is printed as a zero cell, so the device must report EVERY cell with common > 0
     // (threshold +inf); the exact test below drops the ones whose distance does not pass
     const double devDist = dense ? INFINITY : maxDist;
-    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
-    dist_rows(ctx, use64, fl, 0, (uint32_t)numRef, 1, kmer_size, devDist, isContainment, &hits);
-    std::vector<size_t> row_begin;
-    group_by_row(hits, numRef, row_begin);
-
-#pragma omp parallel for num_threads(numThreads) schedule(static, 1)
-    for (int t = 0; t < numThreads; t++) {
-        std::string strBuf;
-        for (size_t i = t; i < numRef; i += numThreads) {
-            fprintf(sub.fpIndexArr[t], "%s\t%s\n", sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
-            for_each_cell(hits, row_begin[i], row_begin[i + 1], i + 1, numRef, dense, [&](size_t j, int common) {
-                const int size0 = (int)sizes[i], size1 = (int)sizes[j];
-                double jorc, d;
-                exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
-                if (d < maxDist)  // strict, dist.cpp:232 / :251
-                    strBuf += sketches[j].fileName + '\t' + sketches[i].fileName + '\t' + to_string(common) + '|' + to_string(size0) + '|' +
-                              to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
-                if (strBuf.size() > (1u << 22)) {
-                    fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
-                    strBuf.clear();
+    // query-row blocks per GPU, balanced on cells + per-row work; every GPU thread walks its block in pieces so that the hit
+    // list stays bounded, formats them with its share of the threads and appends to its own sub-files as it goes
+    const double avg_size = numRef ? (double)fl.off.back() / (double)numRef : 0.0;
+    const std::vector<size_t> bounds = kssd_host::triangle_bounds(numRef, G, 40.0 * avg_size);
+    const size_t piece = std::max<size_t>(64, std::min<size_t>(8192, (size_t)(256u << 20) / std::max<size_t>(numRef, 1)));
+    omp_set_max_active_levels(2);
+#pragma omp parallel for num_threads((int)G) schedule(static, 1)
+    for (size_t g = 0; g < G; g++) {
+        check(kssd_b200_set_max_neighbor(pool.ctx[g], 0), "set_max_neighbor");
+        int f0, nf;
+        files_of_gpu(g, G, numThreads, f0, nf);
+        for (size_t p0 = bounds[g]; p0 < bounds[g + 1]; p0 += piece) {
+            const size_t p1 = std::min(bounds[g + 1], p0 + piece);
+            std::vector<kssd_hit> hits;
+            pool.rows(g, (uint32_t)p0, (uint32_t)p1, 1, kmer_size, devDist, isContainment, &hits);
+            std::vector<size_t> row_begin;
+            group_by_row(hits, p0, p1, row_begin);
+#pragma omp parallel for num_threads(nf) schedule(static, 1)
+            for (int t = 0; t < nf; t++) {
+                std::string strBuf;
+                FILE *out = sub.fpArr[f0 + t];
+                for (size_t i = p0 + ((size_t)t + (size_t)nf - p0 % (size_t)nf) % (size_t)nf; i < p1; i += (size_t)nf) {  // rows with i % nf == t
+                    fprintf(sub.fpIndexArr[f0 + t], "%s\t%s\n", sketches[i].fileName.c_str(), sub.dist_file_list[f0 + t].c_str());
+                    for_each_cell(hits, row_begin[i - p0], row_begin[i - p0 + 1], i + 1, numRef, dense, [&](size_t j, int common) {
+                        const int size0 = (int)sizes[i], size1 = (int)sizes[j];
+                        double jorc, d;
+                        exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
+                        if (d < maxDist)  // strict, dist.cpp:232 / :251
+                            strBuf += sketches[j].fileName + '\t' + sketches[i].fileName + '\t' + to_string(common) + '|' + to_string(size0) + '|' +
+                                      to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
+                        if (strBuf.size() > (1u << 22)) {
+                            fwrite(strBuf.data(), 1, strBuf.size(), out);
+                            strBuf.clear();
+                        }
+                    });
                 }
-            });
-            if (strBuf.size() > (1u << 22)) {
-                fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
-                strBuf.clear();
+                fwrite(strBuf.data(), 1, strBuf.size(), out);
             }
         }
-        fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
     }
-    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
     const double t2 = get_sec();
     std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
     sub.finish();
@@ -327,103 +402,108 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
     const double t0 = get_sec();
     const bool use64 = ref_info.half_k - ref_info.drlevel > 8;  // dist.cpp:435
     std::cerr << (use64 ? "-----use hash64 in index_dist() " : "-----not use hash64 in index_dist() ") << std::endl;
-    IndexFiles ix;
-    read_index(refSketchOut + ".index", refSketchOut + ".dict", "index_dist()", use64, ix);
+    if (numThreads < 1) numThreads = 1;
+    const size_t numQuery = query_sketches.size(), numRef = ref_sketches.size();
     Flat rfl, qfl;
     flatten(ref_sketches, use64, rfl);
     flatten(query_sketches, use64, qfl);
     const std::vector<uint32_t> &rsizes = rfl.sizes, &qsizes = qfl.sizes;
-    kssd_ctx *ctx = kssd_host::context();
-    load_index(ctx, use64, ix, rsizes);
+    GpuPool pool;
+    pool.setup(std::min<size_t>((size_t)numThreads, std::max<size_t>(1, numQuery / min_rows_per_gpu(16))), use64, refSketchOut, "index_dist()", rsizes, qfl);
+    const size_t G = pool.ctx.size();
     const double t1 = get_sec();
     std::cerr << "===================time of read the index and dict sketch file is: " << t1 - t0 << std::endl;
 
-    const size_t numQuery = query_sketches.size();
-    if (numThreads < 1) numThreads = 1;
     SubFiles sub(outputFile, numThreads);
     std::cerr << "=====total: " << numQuery << std::endl;
-
-    // query rows are processed in blocks so that the hit list stays bounded when every cell passes (-D 1.0)
-    const size_t numRef = ref_sketches.size();
-    check(kssd_b200_set_emit_zero_cells(ctx, 0), "set_emit_zero_cells");
     const bool dense = 1.0 <= maxDist;  // zero cells pass `mashD <= maxDist` (dist.cpp:621-624)
     const double devDist = dense ? INFINITY : maxDist;  // dense: the device reports every cell with common > 0 (see index_tridist)
-    // -N: the device selects the maxNeighbor smallest distances (+ ties) of every row among the cells with common > 0;
-    // the bounded max-heap below (dist.cpp:625-640) runs over that superset
-    check(kssd_b200_set_max_neighbor(ctx, isNeighbor ? maxNeighbor : 0), "set_max_neighbor");
-    const size_t block = std::max<size_t>(1, std::min<size_t>(numQuery ? numQuery : 1, (size_t)(64u << 20) / std::max<size_t>(numRef, 1)));
-    for (size_t q0 = 0; q0 < numQuery; q0 += block) {
-        const size_t q1 = std::min(numQuery, q0 + block);
-        std::vector<kssd_hit> hits;
-        dist_rows(ctx, use64, qfl, (uint32_t)q0, (uint32_t)q1, 0, kmer_size, devDist, isContainment, &hits);
-        std::vector<size_t> row_begin;
-        group_by_row(hits, numQuery, row_begin);
-#pragma omp parallel for num_threads(numThreads) schedule(static, 1)
-        for (int t = 0; t < numThreads; t++) {
-            std::string strBuf;
-            for (size_t i = q0 + ((t + numThreads - (int)(q0 % numThreads)) % numThreads); i < q1; i += numThreads) {  // rows with i % numThreads == t
-                fprintf(sub.fpIndexArr[t], "%s\t%s\n", query_sketches[i].fileName.c_str(), sub.dist_file_list[t].c_str());
-                const int size1 = (int)qsizes[i];
-                priority_queue<DistInfo, vector<DistInfo>, cmpDistInfo> curQueue;  // dist.cpp:599
-                auto offer = [&](size_t j, int common) {  // one cell of the reference's j loop (dist.cpp:600-681)
-                    const int size0 = (int)rsizes[j];
-                    double jorc, d;
-                    exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
-                    if (!(d <= maxDist)) return;  // inclusive, dist.cpp:624 / :661
-                    if (isNeighbor) {               // bounded max-heap, dist.cpp:625-640
-                        DistInfo di;
-                        di.refName = ref_sketches[j].fileName;
-                        di.common = common;
-                        di.refSize = size0;
-                        di.jorc = jorc;
-                        di.dist = d;
-                        if (curQueue.size() < maxNeighbor) curQueue.push(di);
-                        else if (d < curQueue.top().dist) {
-                            curQueue.push(di);
-                            curQueue.pop();
-                        }
-                    } else {
-                        strBuf += query_sketches[i].fileName + '\t' + ref_sketches[j].fileName + '\t' + to_string(common) + '|' + to_string(size0) +
-                                  '|' + to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
-                        if (strBuf.size() > (1u << 22)) {
-                            fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
-                            strBuf.clear();
-                        }
-                    }
-                };
-                if (!isNeighbor) {
-                    for_each_cell(hits, row_begin[i], row_begin[i + 1], 0, numRef, dense, offer);  // ascending ref index
-                } else if (maxNeighbor > 0) {
-                    // The same heap operations as the reference's j loop, without walking all numRef columns: a zero cell
-                    // (distance exactly 1.0) changes the heap only while it is not full or while its top is > 1.0, so the
-                    // columns between two reported cells are visited only until then.
-                    size_t j = 0;
-                    for (size_t k = row_begin[i]; k <= row_begin[i + 1]; k++) {
-                        const size_t stop = k < row_begin[i + 1] ? (size_t)hits[k].col : numRef;
-                        if (dense)
-                            for (; j < stop; j++) {
-                                if (curQueue.size() >= maxNeighbor && !(1.0 < curQueue.top().dist)) break;
-                                offer(j, 0);
+    // contiguous blocks of query rows per GPU, walked in pieces so that the hit list stays bounded when every cell passes
+    const std::vector<size_t> bounds = kssd_host::rect_bounds(numQuery, G);
+    const size_t piece = std::max<size_t>(1, std::min<size_t>(numQuery ? numQuery : 1, (size_t)(64u << 20) / std::max<size_t>(numRef, 1)));
+    omp_set_max_active_levels(2);
+#pragma omp parallel for num_threads((int)G) schedule(static, 1)
+    for (size_t g = 0; g < G; g++) {
+        // -N: the device selects the maxNeighbor smallest distances (+ ties) of every row among the cells with common > 0;
+        // the bounded max-heap below (dist.cpp:625-640) runs over that superset
+        check(kssd_b200_set_max_neighbor(pool.ctx[g], isNeighbor ? maxNeighbor : 0), "set_max_neighbor");
+        int f0, nf;
+        files_of_gpu(g, G, numThreads, f0, nf);
+        for (size_t q0 = bounds[g]; q0 < bounds[g + 1]; q0 += piece) {
+            const size_t q1 = std::min(bounds[g + 1], q0 + piece);
+            std::vector<kssd_hit> hits;
+            pool.rows(g, (uint32_t)q0, (uint32_t)q1, 0, kmer_size, devDist, isContainment, &hits);
+            std::vector<size_t> row_begin;
+            group_by_row(hits, q0, q1, row_begin);
+#pragma omp parallel for num_threads(nf) schedule(static, 1)
+            for (int t = 0; t < nf; t++) {
+                std::string strBuf;
+                FILE *out = sub.fpArr[f0 + t];
+                for (size_t i = q0 + ((size_t)t + (size_t)nf - q0 % (size_t)nf) % (size_t)nf; i < q1; i += (size_t)nf) {  // rows with i % nf == t
+                    fprintf(sub.fpIndexArr[f0 + t], "%s\t%s\n", query_sketches[i].fileName.c_str(), sub.dist_file_list[f0 + t].c_str());
+                    const int size1 = (int)qsizes[i];
+                    const size_t kb = row_begin[i - q0], ke = row_begin[i - q0 + 1];
+                    priority_queue<DistInfo, vector<DistInfo>, cmpDistInfo> curQueue;  // dist.cpp:599
+                    auto offer = [&](size_t j, int common) {  // one cell of the reference's j loop (dist.cpp:600-681)
+                        const int size0 = (int)rsizes[j];
+                        double jorc, d;
+                        exact_distance(common, size0, size1, kmer_size, isContainment, jorc, d);
+                        if (!(d <= maxDist)) return;  // inclusive, dist.cpp:624 / :661
+                        if (isNeighbor) {               // bounded max-heap, dist.cpp:625-640
+                            DistInfo di;
+                            di.refName = ref_sketches[j].fileName;
+                            di.common = common;
+                            di.refSize = size0;
+                            di.jorc = jorc;
+                            di.dist = d;
+                            if (curQueue.size() < maxNeighbor) curQueue.push(di);
+                            else if (d < curQueue.top().dist) {
+                                curQueue.push(di);
+                                curQueue.pop();
                             }
-                        if (k < row_begin[i + 1]) offer(stop, (int)hits[k].common);
-                        j = stop + 1;
+                        } else {
+                            strBuf += query_sketches[i].fileName + '\t' + ref_sketches[j].fileName + '\t' + to_string(common) + '|' + to_string(size0) +
+                                      '|' + to_string(size1) + '\t' + to_string(jorc) + '\t' + to_string(d) + '\n';
+                            if (strBuf.size() > (1u << 22)) {
+                                fwrite(strBuf.data(), 1, strBuf.size(), out);
+                                strBuf.clear();
+                            }
+                        }
+                    };
+                    if (!isNeighbor) {
+                        for_each_cell(hits, kb, ke, 0, numRef, dense, offer);  // ascending ref index
+                    } else if (maxNeighbor > 0) {
+                        // The same heap operations as the reference's j loop, without walking all numRef columns: a zero cell
+                        // (distance exactly 1.0) changes the heap only while it is not full or while its top is > 1.0, so the
+                        // columns between two reported cells are visited only until then.
+                        size_t j = 0;
+                        for (size_t k = kb; k <= ke; k++) {
+                            const size_t stop = k < ke ? (size_t)hits[k].col : numRef;
+                            if (dense)
+                                for (; j < stop; j++) {
+                                    if (curQueue.size() >= maxNeighbor && !(1.0 < curQueue.top().dist)) break;
+                                    offer(j, 0);
+                                }
+                            if (k < ke) offer(stop, (int)hits[k].common);
+                            j = stop + 1;
+                        }
+                    }
+                    while (!curQueue.empty()) {  // drained largest first, dist.cpp:683-689
+                        const DistInfo di = curQueue.top();
+                        strBuf += query_sketches[i].fileName + '\t' + di.refName + '\t' + to_string(di.common) + '|' + to_string(di.refSize) + '|' +
+                                  to_string(size1) + '\t' + to_string(di.jorc) + '\t' + to_string(di.dist) + '\n';
+                        curQueue.pop();
+                    }
+                    if (strBuf.size() > (1u << 22)) {
+                        fwrite(strBuf.data(), 1, strBuf.size(), out);
+                        strBuf.clear();
                     }
                 }
-                while (!curQueue.empty()) {  // drained largest first, dist.cpp:683-689
-                    const DistInfo di = curQueue.top();
-                    strBuf += query_sketches[i].fileName + '\t' + di.refName + '\t' + to_string(di.common) + '|' + to_string(di.refSize) + '|' +
-                              to_string(size1) + '\t' + to_string(di.jorc) + '\t' + to_string(di.dist) + '\n';
-                    curQueue.pop();
-                }
-                if (strBuf.size() > (1u << 22)) {
-                    fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
-                    strBuf.clear();
-                }
+                fwrite(strBuf.data(), 1, strBuf.size(), out);
             }
-            fwrite(strBuf.data(), 1, strBuf.size(), sub.fpArr[t]);
         }
+        check(kssd_b200_set_max_neighbor(pool.ctx[g], 0), "set_max_neighbor");
     }
-    check(kssd_b200_set_max_neighbor(ctx, 0), "set_max_neighbor");
     const double t2 = get_sec();
     std::cerr << "===================time of multiple threads distance computing and save the subFile is: " << t2 - t1 << std::endl;
     sub.finish();

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cerrno>
+#include <condition_variable>
 #include <cstring>
 #include <fstream>
 #include <mutex>
@@ -39,47 +40,71 @@ using kssd_host::check;
 
 const unsigned char kSeparator = '\n';  // any non-ACGT byte resets the valid-run counter like a new record does
 
-// Packs pieces (whole records of one genome, separator-terminated) into the library's pinned batches.
+// Packs pieces (whole records of one genome, separator-terminated) into the library's pinned batches.  A parser thread
+// RESERVES a slice of the current batch under the lock and copies into it outside the lock, so the copies of all parser
+// threads run in parallel; a batch is submitted once its last writer has finished.
 class BatchFiller {
   public:
     BatchFiller(kssd_ctx *ctx, bool has_qual) : ctx_(ctx), has_qual_(has_qual) {}
 
-    void append(uint32_t genome, const std::vector<unsigned char> &seq, const std::vector<unsigned char> &qual) {
-        const size_t n = seq.size();
-        if (n == 0) return;
-        std::lock_guard<std::mutex> lock(mu_);
-        if (cur_ && (cur_->n_bytes + n > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit();
-        if (!cur_) {
-            check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, n), 1 << 16), "batch_acquire");
-            cur_->n_bytes = 0;
-            cur_->n_seg = 0;
-            cur_->first_emit = 0;
+    // seq[0, n) (+ qual) of `genome`; when `terminate` one separator byte is appended after the bytes
+    void append(uint32_t genome, const unsigned char *seq, const unsigned char *qual, size_t n, bool terminate) {
+        const size_t need = n + (terminate ? 1 : 0);
+        if (need == 0) return;
+        kssd_batch *b;
+        size_t at;
+        {
+            std::unique_lock<std::mutex> lock(mu_);
+            if (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
+            if (!cur_) {
+                check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, need), 1 << 16), "batch_acquire");
+                cur_->n_bytes = 0;
+                cur_->n_seg = 0;
+                cur_->first_emit = 0;
+            }
+            b = cur_;
+            at = b->n_bytes;
+            b->seg_off[b->n_seg] = at;
+            b->seg_genome[b->n_seg] = genome;
+            b->n_seg++;
+            b->n_bytes += need;
+            b->seg_off[b->n_seg] = b->n_bytes;
+            writers_++;
         }
-        memcpy(cur_->seq + cur_->n_bytes, seq.data(), n);
-        if (has_qual_) memcpy(cur_->qual + cur_->n_bytes, qual.data(), n);
-        cur_->seg_off[cur_->n_seg] = cur_->n_bytes;
-        cur_->seg_genome[cur_->n_seg] = genome;
-        cur_->n_seg++;
-        cur_->n_bytes += n;
-        cur_->seg_off[cur_->n_seg] = cur_->n_bytes;
+        memcpy(b->seq + at, seq, n);
+        if (terminate) b->seq[at + n] = kSeparator;
+        if (has_qual_) {
+            if (qual) memcpy(b->qual + at, qual, n);
+            else memset(b->qual + at, 0x7F, n);
+            if (terminate) b->qual[at + n] = 0x7F;
+        }
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            writers_--;
+        }
+        cv_.notify_all();
     }
 
     void flush() {
-        std::lock_guard<std::mutex> lock(mu_);
-        if (cur_) submit();
+        std::unique_lock<std::mutex> lock(mu_);
+        if (cur_) submit(lock);
     }
 
     static constexpr size_t kBatchBytes = 256u << 20;  // pinned batch size
-    static constexpr size_t kPieceBytes = 32u << 20;   // a parser thread hands over at most this much at a time
+    static constexpr size_t kPieceBytes = 8u << 20;    // small records are gathered per thread up to this much
+    static constexpr size_t kDirectBytes = 1u << 20;   // records at least this long go straight from the parser's buffer
 
   private:
-    void submit() {
+    void submit(std::unique_lock<std::mutex> &lock) {  // all slices of cur_ are reserved by now: wait for their copies
+        cv_.wait(lock, [&] { return writers_ == 0; });
         if (cur_->n_bytes) check(kssd_b200_batch_submit(ctx_, cur_), "batch_submit");
         cur_ = nullptr;
     }
     kssd_ctx *ctx_;
     bool has_qual_;
     std::mutex mu_;
+    std::condition_variable cv_;
+    int writers_ = 0;  // slices reserved in cur_ whose copy has not finished
     kssd_batch *cur_ = nullptr;
 };
 
@@ -106,53 +131,77 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     const size_t n = fileList.size();
     std::cerr << "the total fileNumber is: " << n << std::endl;
 
-    kssd_ctx *ctx = kssd_host::context();
-    check(kssd_b200_set_params(ctx, p.half_k, p.half_subk, p.drlevel, p.shuffled_dim), "set_params");
-    check(kssd_b200_sketch_begin(ctx, (uint32_t)n, fastq ? 1 : 0, leastQual, leastNumKmer), "sketch_begin");
-    BatchFiller filler(ctx, fastq);
+    // one context per GPU; file t (position in the size-descending list) goes to GPU t % G, which balances the bytes
+    const size_t G = std::max<size_t>(1, std::min(kssd_host::device_count(), n));
+    std::vector<kssd_ctx *> ctxs(G);
+    for (size_t g = 0; g < G; g++) ctxs[g] = kssd_host::context_at(g);
+#pragma omp parallel for num_threads((int)G) schedule(static, 1)
+    for (size_t g = 0; g < G; g++) {  // the table build walks all 16^half_subk entries: one host thread per context
+        check(kssd_b200_set_params(ctxs[g], p.half_k, p.half_subk, p.drlevel, p.shuffled_dim), "set_params");
+        check(kssd_b200_sketch_begin(ctxs[g], (uint32_t)n, fastq ? 1 : 0, leastQual, leastNumKmer), "sketch_begin");
+    }
+    std::vector<BatchFiller *> fillers(G);
+    for (size_t g = 0; g < G; g++) fillers[g] = new BatchFiller(ctxs[g], fastq);
 
     if (numThreads < 1) numThreads = 1;
 #pragma omp parallel for num_threads(numThreads) schedule(dynamic)
     for (size_t t = 0; t < n; t++) {
         gzFile fp = gzopen(fileList[t].fileName.c_str(), "r");
         if (fp == NULL) err(errno, "cannot open the genome file: %s\n", fileList[t].fileName.c_str());
+        gzbuffer(fp, 1 << 20);
         kseq_t *ks = kseq_init(fp);
-        std::vector<unsigned char> seq, qual;
+        BatchFiller &filler = *fillers[t % G];
+        std::vector<unsigned char> seq, qual;  // small records of this genome, gathered
         while (true) {
             const int length = kseq_read(ks);  // int, as in the reference (sketch.cpp:475): one record < 2^31 bases
             if (length < 0) break;
+            const size_t ql = fastq && ks->qual.s ? std::min<size_t>(ks->qual.l, (size_t)length) : 0;
+            if ((size_t)length >= BatchFiller::kDirectBytes && (!fastq || ql == (size_t)length)) {
+                if (!seq.empty()) {
+                    filler.append((uint32_t)t, seq.data(), fastq ? qual.data() : nullptr, seq.size(), false);
+                    seq.clear();
+                    qual.clear();
+                }
+                filler.append((uint32_t)t, (const unsigned char *)ks->seq.s, fastq ? (const unsigned char *)ks->qual.s : nullptr, (size_t)length, true);
+                continue;
+            }
             const size_t at = seq.size();
             seq.resize(at + (size_t)length + 1);
             memcpy(seq.data() + at, ks->seq.s, (size_t)length);
             seq[at + length] = kSeparator;
             if (fastq) {
                 qual.resize(at + (size_t)length + 1);
-                const size_t ql = ks->qual.s ? std::min<size_t>(ks->qual.l, (size_t)length) : 0;
                 if (ql) memcpy(qual.data() + at, ks->qual.s, ql);
                 memset(qual.data() + at + ql, 0x7F, (size_t)length + 1 - ql);  // no quality string: nothing is filtered
             }
             if (seq.size() >= BatchFiller::kPieceBytes) {
-                filler.append((uint32_t)t, seq, qual);
+                filler.append((uint32_t)t, seq.data(), fastq ? qual.data() : nullptr, seq.size(), false);
                 seq.clear();
                 qual.clear();
             }
         }
-        filler.append((uint32_t)t, seq, qual);
+        if (!seq.empty()) filler.append((uint32_t)t, seq.data(), fastq ? qual.data() : nullptr, seq.size(), false);
         kseq_destroy(ks);
         gzclose(fp);
     }
-    filler.flush();
 
-    const uint32_t *hashes = nullptr;
-    const uint64_t *hashes64 = nullptr, *off = nullptr;
-    if (use64) check(kssd_b200_sketch_finish64(ctx, &hashes64, &off), "sketch_finish64");
-    else check(kssd_b200_sketch_finish(ctx, &hashes, &off), "sketch_finish");
+    std::vector<const uint32_t *> hashes(G, nullptr);
+    std::vector<const uint64_t *> hashes64(G, nullptr), off(G, nullptr);
+#pragma omp parallel for num_threads((int)G) schedule(static, 1)
+    for (size_t g = 0; g < G; g++) {
+        fillers[g]->flush();
+        if (use64) check(kssd_b200_sketch_finish64(ctxs[g], &hashes64[g], &off[g]), "sketch_finish64");
+        else check(kssd_b200_sketch_finish(ctxs[g], &hashes[g], &off[g]), "sketch_finish");
+        delete fillers[g];
+    }
+    sketches.reserve(sketches.size() + n);
     for (size_t t = 0; t < n; t++) {
+        const size_t g = t % G;
         sketch_t s;
         s.fileName = fileList[t].fileName;
         s.id = (int)t;
-        if (use64) s.hashSet64.assign(hashes64 + off[t], hashes64 + off[t + 1]);
-        else s.hashSet.assign(hashes + off[t], hashes + off[t + 1]);
+        if (use64) s.hashSet64.assign(hashes64[g] + off[g][t], hashes64[g] + off[g][t + 1]);
+        else s.hashSet.assign(hashes[g] + off[g][t], hashes[g] + off[g][t + 1]);
         sketches.push_back(s);
     }
 
@@ -196,6 +245,9 @@ void transSketches(vector<sketch_t> &sketches, sketchInfo_t &info, string dictFi
     std::vector<uint64_t> off(sketches.size() + 1, 0);
     for (size_t i = 0; i < sketches.size(); i++) off[i + 1] = off[i] + (use64 ? sketches[i].hashSet64.size() : sketches[i].hashSet.size());
     kssd_ctx *ctx = kssd_host::context();
+    kssd_host::IndexCache &cache = kssd_host::index_cache();
+    cache.valid = false;
+    kssd_host::pending_writes().wait(&indexFile);  // an earlier background write of the same file
     auto open_or_die = [](const std::string &path, const char *what) {
         FILE *f = fopen(path.c_str(), "w+");
         if (!f) {
@@ -225,6 +277,7 @@ void transSketches(vector<sketch_t> &sketches, sketchInfo_t &info, string dictFi
         fwrite(uniq_hash, sizeof(uint64_t), hash_number, fp1);
         fwrite(uniq_count, sizeof(uint32_t), hash_number, fp1);
         fclose(fp1);
+        cache = kssd_host::IndexCache{true, true, indexFile, dictFile, sketches.size()};
         return;
     }
     const size_t hashSize = 1LLU << (4 * (info.half_k - info.drlevel));
@@ -242,19 +295,30 @@ void transSketches(vector<sketch_t> &sketches, sketchInfo_t &info, string dictFi
     fwrite(dict, sizeof(uint32_t), total, fp0);
     fclose(fp0);
 
-    uint32_t *counts = (uint32_t *)calloc(hashSize, sizeof(uint32_t));  // the format wants the dense array
-    for (uint64_t u = 0; u < n_uniq; u++) {
-        if (uniq_hash[u] >= hashSize) {
-            std::cerr << "ERROR: transSketches, hash " << uniq_hash[u] << " outside the hash space " << hashSize << std::endl;
-            exit(1);
-        }
-        counts[uniq_hash[u]] = uniq_count[u];
-    }
+    // The format wants the dense 2^(4(k-l))-entry count array (1 GiB for L3K10), almost all zeros.  It is produced by a
+    // background thread: a distance step that follows in this process (alldist / dist on a genome list) works on the CSR
+    // that is still resident on the device instead of reading the file back (kssd_host::index_cache).
     FILE *fp1 = open_or_die(indexFile, "indexFile");
     const uint64_t totalIndex = total;
-    fwrite(&hashSize, sizeof(size_t), 1, fp1);
-    fwrite(&totalIndex, sizeof(uint64_t), 1, fp1);
-    fwrite(counts, sizeof(uint32_t), hashSize, fp1);
-    fclose(fp1);
-    free(counts);
+    std::vector<uint32_t> uh(uniq_hash, uniq_hash + n_uniq), uc(uniq_count, uniq_count + n_uniq);
+    for (uint64_t u = 0; u < n_uniq; u++)
+        if (uh[u] >= hashSize) {
+            std::cerr << "ERROR: transSketches, hash " << uh[u] << " outside the hash space " << hashSize << std::endl;
+            exit(1);
+        }
+    kssd_host::pending_writes().add(indexFile, std::thread([fp1, hashSize, totalIndex, uh = std::move(uh), uc = std::move(uc)]() {
+        fwrite(&hashSize, sizeof(size_t), 1, fp1);
+        fwrite(&totalIndex, sizeof(uint64_t), 1, fp1);
+        const size_t kChunk = 1u << 22;  // 16 MiB of counters at a time: no 1 GiB allocation
+        std::vector<uint32_t> counts(std::min<size_t>(kChunk, hashSize));
+        size_t u = 0;
+        for (size_t h0 = 0; h0 < hashSize; h0 += kChunk) {
+            const size_t h1 = std::min(hashSize, h0 + kChunk);
+            std::fill(counts.begin(), counts.begin() + (h1 - h0), 0u);
+            for (; u < uh.size() && uh[u] < h1; u++) counts[uh[u] - h0] = uc[u];  // distinct hashes ascend
+            fwrite(counts.data(), sizeof(uint32_t), h1 - h0, fp1);
+        }
+        fclose(fp1);
+    }));
+    cache = kssd_host::IndexCache{true, false, indexFile, dictFile, sketches.size()};
 }

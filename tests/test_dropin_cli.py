@@ -221,3 +221,98 @@ def test_64bit_hash_configuration_k12(work):
         shutil.copy(os.path.join(ndir, "mine" + ext), os.path.join(rdir, "w.sketch" + ext))
     _run(REF, ["alldist", "-i", "w.sketch", "-D", "0.3", "-o", "w2.alldist", "-t", "3"], rdir)
     assert la == sorted(formats.parse_dist_text(os.path.join(rdir, "w2.alldist")))
+
+
+def _run_env(binary, args, cwd, env):
+    e = dict(os.environ)
+    e.update(env)
+    p = subprocess.run([binary] + args, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600, env=e)
+    assert p.returncode == 0, f"{os.path.basename(binary)} {' '.join(args)} failed:\n{p.stdout.decode()[-3000:]}"
+    return p.stdout.decode()
+
+
+def test_index_stays_on_device_and_files_are_still_written(work):
+    """alldist -i <genome list> in one process: the distance step uses the CSR transSketches left on the device (no read-back
+    of the 1 GiB .index), while the .index / .dict files are still produced -- a second run that starts from the .sketch
+    reads them from disk and must print the same lines; the dense .index is what the reference's reader expects."""
+    d, ndir = work["d"], work["dirs"]["new"]
+    lst = os.path.join(ndir, "mylist")
+    shutil.copy(os.path.join(d, "refs.list"), lst)
+    out = _run(NEW, ["alldist", "-L", os.path.join(d, "L3K10.shuf"), "-i", "mylist", "-D", "0.08", "-o", "c1.alldist", "-t", "4"], ndir)
+    assert "is not read back" in out
+    counts, postings = formats.read_index_dict(os.path.join(ndir, "mylist.sketch.index"), os.path.join(ndir, "mylist.sketch.dict"))
+    assert len(counts) == 1 << 28 and int(counts.sum()) == len(postings)
+    out2 = _run(NEW, ["alldist", "-i", "mylist.sketch", "-D", "0.08", "-o", "c2.alldist", "-t", "4"], ndir)
+    assert "is not read back" not in out2
+    l1 = sorted(formats.parse_dist_text(os.path.join(ndir, "c1.alldist")))
+    assert len(l1) >= 8 and l1 == sorted(formats.parse_dist_text(os.path.join(ndir, "c2.alldist")))
+    # and the reference reads the files the drop-in wrote
+    rdir = work["dirs"]["ref"]
+    for f in ("mylist.sketch", "mylist.sketch.index", "mylist.sketch.dict"):
+        shutil.copy(os.path.join(ndir, f), os.path.join(rdir, f))
+    _run(REF, ["alldist", "-i", "mylist.sketch", "-D", "0.08", "-o", "c3.alldist", "-t", "4"], rdir)
+    assert l1 == sorted(formats.parse_dist_text(os.path.join(rdir, "c3.alldist")))
+
+
+def test_output_split_into_subfiles(work):
+    """The > 4 GiB branch of the result-file policy (src/dist.cpp:314-336): sub-files kept in <out>.dir, <out>.index maps
+    every genome to its sub-file.  Taken here with KSSD_B200_MERGE_LIMIT (the real 4 GiB case is run by bench C5)."""
+    d, ndir, rdir = work["d"], work["dirs"]["new"], work["dirs"]["ref"]
+    if not os.path.exists(os.path.join(rdir, "refs.sketch")):
+        _run(REF, ["sketch", "-L", os.path.join(d, "L3K10.shuf"), "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"], rdir)
+    for f in ("s.sketch.index", "s.sketch.dict"):
+        if os.path.exists(os.path.join(ndir, f)):
+            os.remove(os.path.join(ndir, f))
+    shutil.copy(os.path.join(rdir, "refs.sketch"), os.path.join(ndir, "s.sketch"))
+    _run(NEW, ["alldist", "-i", "s.sketch", "-D", "0.5", "-o", "whole.alldist", "-t", "3"], ndir)
+    _run_env(NEW, ["alldist", "-i", "s.sketch", "-D", "0.5", "-o", "split.alldist", "-t", "3"], ndir, {"KSSD_B200_MERGE_LIMIT": "100"})
+    assert not os.path.exists(os.path.join(ndir, "split.alldist"))
+    sub = sorted(os.listdir(os.path.join(ndir, "split.alldist.dir")))
+    assert sub == ["split.alldist.0", "split.alldist.1", "split.alldist.2"]
+    lines = []
+    for f in sub:
+        lines += formats.parse_dist_text(os.path.join(ndir, "split.alldist.dir", f))
+    whole = sorted(formats.parse_dist_text(os.path.join(ndir, "whole.alldist")))
+    assert len(whole) >= 8 and sorted(lines) == whole
+    with open(os.path.join(ndir, "split.alldist.index")) as f:
+        idx = f.read().splitlines()
+    _, names, _ = formats.read_sketch(os.path.join(ndir, "s.sketch"))
+    assert idx[0] == "genomeName\tdistFileName"
+    got = dict(x.split("\t") for x in idx[1:])
+    assert sorted(got) == sorted(names)
+    for a, b, *_ in lines:  # a line "name_j name_i ..." lives in the sub-file of its row genome (name_i)
+        pass
+    for f in sub:
+        rows_here = {b for a, b, *_ in formats.parse_dist_text(os.path.join(ndir, "split.alldist.dir", f))}
+        assert all(got[r].endswith(f) for r in rows_here)
+
+
+def test_multi_gpu_cli_equals_reference(work):
+    """One context per visible GPU inside the drop-in (files dealt over the GPUs for sketching, query rows sharded for
+    alldist / dist with the index copied device to device): same files as the reference.  Needs >= 2 GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    d, ndir, rdir = work["d"], work["dirs"]["new"], work["dirs"]["ref"]
+    shuf = os.path.join(d, "L3K10.shuf")
+    out = _run_env(NEW, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "mg", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all"})
+    one = _run_env(NEW, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "sg", "-t", "4"], ndir, {"KSSD_B200_DEVICE": "0"})
+    a, b = _sketch_sets(os.path.join(ndir, "mg.sketch")), _sketch_sets(os.path.join(ndir, "sg.sketch"))
+    assert sorted(a) == sorted(b) and all(np.array_equal(a[n], b[n]) for n in a)
+    if not os.path.exists(os.path.join(rdir, "refs.sketch")):
+        _run(REF, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"], rdir)
+    if not os.path.exists(os.path.join(rdir, "queries.sketch")):
+        _run(REF, ["sketch", "-q", "-L", shuf, "-i", os.path.join(d, "queries.list"), "-o", "queries", "-t", "4"], rdir)
+    for tag in ("ref", "new"):
+        for f in ("m.sketch.index", "m.sketch.dict"):
+            if os.path.exists(os.path.join(work["dirs"][tag], f)):
+                os.remove(os.path.join(work["dirs"][tag], f))
+        shutil.copy(os.path.join(rdir, "refs.sketch"), os.path.join(work["dirs"][tag], "m.sketch"))
+        shutil.copy(os.path.join(rdir, "queries.sketch"), os.path.join(work["dirs"][tag], "mq.sketch"))
+    _run(REF, ["alldist", "-i", "m.sketch", "-D", "0.5", "-o", "m.alldist", "-t", "4"], rdir)
+    _run_env(NEW, ["alldist", "-i", "m.sketch", "-D", "0.5", "-o", "m.alldist", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_MIN_ROWS_PER_GPU": "2"})
+    assert sorted(formats.parse_dist_text(os.path.join(rdir, "m.alldist"))) == sorted(formats.parse_dist_text(os.path.join(ndir, "m.alldist")))
+    for extra in (["-D", "0.3"], ["-N", "2"], []):
+        _run(REF, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, rdir)
+        _run_env(NEW, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_MIN_ROWS_PER_GPU": "2"})
+        assert sorted(formats.parse_dist_text(os.path.join(rdir, "m.dist"))) == sorted(formats.parse_dist_text(os.path.join(ndir, "m.dist")))
