@@ -29,6 +29,7 @@ extern "C" {
 #define KSSD_E_ARG (-2)         /* bad argument / call order */
 #define KSSD_E_UNSUPPORTED (-3) /* shape the library does not implement (half_k > 12, >= 2^32 postings); the text says which */
 #define KSSD_E_PARAM (-4)       /* half_subk - drlevel < 3: the reference aborts here (common.cpp:37-39) */
+#define KSSD_E_SYNTAX (-6)      /* raw FASTA text that kseq would not read as plain FASTA (sketch_finish): parse it on the host */
 #define KSSD_E_OVERFLOW (-5)    /* an output buffer stayed too small after regrowing; text says which and the size needed */
 
 typedef struct kssd_ctx kssd_ctx;
@@ -72,6 +73,8 @@ int kssd_b200_set_relax_guard(kssd_ctx *ctx, int on);
  * The first byte after a genome's last record must also be a separator (or the end of the batch).
  * A record continued from the previous batch is prefixed by its last 2*half_k-1 bytes and first_emit is set
  * to that count: k-mers ending before first_emit are context only. */
+#define KSSD_SEG_IN_HEADER 1
+#define KSSD_SEG_MID_LINE 2
 typedef struct kssd_batch {
     uint8_t *seq;         /* pinned, library owned, capacity bytes */
     uint8_t *qual;        /* pinned, same layout; used only when the session was begun with has_qual */
@@ -83,6 +86,20 @@ typedef struct kssd_batch {
     uint32_t n_seg;       /* filled by caller */
     uint64_t first_emit;  /* filled by caller (0 when nothing is continued) */
     void *priv;
+    /* Raw FASTA text, tokenised ON THE DEVICE (replaces kseq's record loop, src/kseq.h:175-215, and RabbitFX's formatter,
+     * RabbitFX/io/Formater.cpp:87-129, for plain uncompressed FASTA): raw_fasta = 1 and seq holds PIECES of file text instead
+     * of parsed records.  Piece i = bytes [seg_off[i], seg_off[i+1]) of genome seg_genome[i]; seg_off[i] is a multiple of 32
+     * (pad the end of a piece with '\n'; a piece must not end with a '\r' whose '\n' is in the next one).  A piece is a whole
+     * file, or a slice of a large one that begins at a line start (seg_flags[i] = 0), inside a header line (KSSD_SEG_IN_HEADER)
+     * or inside a sequence line (KSSD_SEG_MID_LINE); a slice that continues a record is prefixed with the last
+     * >= 2*half_k - 1 sequence bytes before it (plus a '\n' when the slice itself begins at a line start) and seg_first[i] =
+     * length of that prefix: k-mers ending inside it were already found by the previous slice.  Header lines become one
+     * separator byte.  Text kseq would not
+     * take as plain FASTA (a line starting with '+' after a header / sequence line) makes sketch_finish return
+     * KSSD_E_SYNTAX.  Not for sessions with quality. */
+    int raw_fasta;        /* filled by caller; batch_acquire resets it to 0 */
+    uint8_t *seg_flags;   /* pinned, seg_capacity entries */
+    uint32_t *seg_first;  /* pinned, seg_capacity entries */
 } kssd_batch;
 
 /* Start a sketch session for n_genomes genomes.  least_qual / least_num_kmer are the -Q / -n options

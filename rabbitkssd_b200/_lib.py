@@ -20,7 +20,7 @@ class Hit(C.Structure):
 class Batch(C.Structure):
     _fields_ = [("seq", u8p), ("qual", u8p), ("capacity", C.c_uint64), ("n_bytes", C.c_uint64),
                 ("seg_off", u64p), ("seg_genome", u32p), ("seg_capacity", C.c_uint32), ("n_seg", C.c_uint32),
-                ("first_emit", C.c_uint64), ("priv", C.c_void_p)]
+                ("first_emit", C.c_uint64), ("priv", C.c_void_p), ("raw_fasta", C.c_int), ("seg_flags", u8p), ("seg_first", u32p)]
 
 
 SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(Hit), C.c_size_t)

@@ -110,6 +110,35 @@ class Context:
         bt.first_emit = first_emit
         check(self.lib.kssd_b200_batch_submit(self.h, b))
 
+    def submit_raw_fasta(self, pieces):
+        """One batch of RAW FASTA text, tokenised on the device.  pieces: list of (genome, text bytes / uint8 array, flags (0 line
+        start, 1 inside a header line, 2 inside a sequence line), first) -- see kssd_batch.raw_fasta in include/kssd_b200.h.
+        Every piece is padded with newlines to a multiple of 32."""
+        sizes = [(len(t) + 31) // 32 * 32 for _, t, _, _ in pieces]
+        total = sum(sizes)
+        b = C.POINTER(_lib.Batch)()
+        check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), total, len(pieces)))
+        bt = b.contents
+        buf = np.full(total, 10, dtype=np.uint8)
+        off = np.zeros(len(pieces) + 1, dtype=np.uint64)
+        at = 0
+        for i, ((g, t, fl, first), sz) in enumerate(zip(pieces, sizes)):
+            t = np.frombuffer(bytes(t), dtype=np.uint8) if not isinstance(t, np.ndarray) else t
+            buf[at:at + len(t)] = t
+            off[i] = at
+            bt.seg_genome[i] = g
+            bt.seg_flags[i] = int(fl)
+            bt.seg_first[i] = first
+            at += sz
+        off[len(pieces)] = at
+        C.memmove(bt.seq, buf.ctypes.data, total)
+        C.memmove(bt.seg_off, off.ctypes.data, off.nbytes)
+        bt.n_bytes = total
+        bt.n_seg = len(pieces)
+        bt.first_emit = 0
+        bt.raw_fasta = 1
+        check(self.lib.kssd_b200_batch_submit(self.h, b))
+
     def acquire_batch(self, min_capacity, min_segments):
         b = C.POINTER(_lib.Batch)()
         check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), min_capacity, min_segments))

@@ -174,14 +174,23 @@ void kssd_b200_destroy(kssd_ctx *c) {
     for (DevBuf *b : dev) b->release();
     HostBuf *host[] = {&c->h_hashes, &c->h_genome_off, &c->h_scalar, &c->h_uniq_hash, &c->h_uniq_count, &c->h_dict, &c->h_hits, &c->h_snap, &c->h_hashes64, &c->h_uniq_hash64};
     for (HostBuf *b : host) b->release();
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < kssd_ctx::kBatches; i++) {
         c->bpriv[i].seq.release();
         c->bpriv[i].qual.release();
         c->bpriv[i].seg_off.release();
         c->bpriv[i].seg_genome.release();
+        c->bpriv[i].seg_flags.release();
+        c->bpriv[i].seg_first.release();
         if (c->batches_init) cudaEventDestroy(c->bpriv[i].h2d_done);
-        if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
     }
+    for (int i = 0; i < 2; i++) {
+        if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
+        c->d_stage_raw[i].release();
+        c->d_stage_rawseg[i].release();
+        c->d_stage_cseg[i].release();
+    }
+    c->d_fa_scratch.release();
+    c->d_filter.release();
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     delete c;

@@ -70,6 +70,7 @@ struct ReplayItem {
     const uint32_t *seg_genome;
     uint32_t n_seg;
     uint64_t first_emit, chunk_bytes;
+    const uint64_t *seg_first;  // raw-text batches: per-segment first new position (device), else null
 };
 
 struct TimedLaunches {
@@ -86,7 +87,8 @@ struct TimedLaunches {
 struct kssd_batch_priv {
     cudaEvent_t h2d_done;
     bool in_flight = false;
-    kssd::HostBuf seq, qual, seg_off, seg_genome;
+    bool held = false;  // acquired and not yet submitted
+    kssd::HostBuf seq, qual, seg_off, seg_genome, seg_flags, seg_first;
 };
 
 namespace kssd {
@@ -126,6 +128,7 @@ struct kssd_ctx {
     std::vector<kssd::ReplayItem> replay;  // scans not yet verified against the emit capacity, in submission order
     uint64_t verified_cursor = 0;          // emit cursor after the last verified scan
     bool replaying = false;
+    bool raw_text_seen = false;            // the session took raw FASTA text (fasta.cu)
     kssd::HostBuf h_snap;                  // pinned: emit cursor after the last scan of staging buffer 0 / 1
     kssd::DevBuf d_emit;      // u64 keys (genome<<32 | hash)
     kssd::DevBuf d_emit_rank; // u32 rank of each key inside its genome
@@ -135,10 +138,13 @@ struct kssd_ctx {
     kssd::DevBuf d_gcount;    // u32 emitted keys per genome (written by the scan kernel)
     kssd::DevBuf d_seg_start, d_ucount;  // per-genome segment starts (u64), unique counts
     kssd::DevBuf d_stage_seq[2], d_stage_qual[2], d_stage_segoff[2], d_stage_seggen[2];
+    // raw FASTA text batches (fasta.cu): the raw bytes + piece table of a batch, the compacted piece table; scratch
+    kssd::DevBuf d_stage_raw[2], d_stage_rawseg[2], d_stage_cseg[2], d_fa_scratch;
     cudaEvent_t stage_free[2] = {nullptr, nullptr};
     int stage_next = 0;
-    kssd_batch batches[2];
-    kssd_batch_priv bpriv[2];
+    static constexpr int kBatches = 4;  // pinned batches: a host may fill two kinds (parsed records, raw text) while two are in flight
+    kssd_batch batches[kBatches];
+    kssd_batch_priv bpriv[kBatches];
     bool batches_init = false;
     int batch_next = 0;
     kssd::DevBuf d_sort_tmp, d_sort_counts, d_keys_unique;
@@ -191,7 +197,10 @@ namespace kssd {
 // sketch.cu
 int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
                 const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit,
-                uint64_t pos_base = 0);
+                uint64_t pos_base = 0, const uint64_t *d_seg_first = nullptr);
+// fasta.cu
+int fasta_tokenise(kssd_ctx *c, const uint8_t *d_raw, uint64_t n_raw, const uint64_t *d_seg_off, const uint8_t *d_seg_flags, const uint32_t *d_seg_first,
+                   uint32_t n_seg, uint8_t *d_out, uint64_t *d_cseg_off, uint64_t *d_cseg_first, uint32_t *d_anomaly, uint64_t *out_bytes);
 int build_tables(kssd_ctx *c, const int32_t *shuffled_dim);
 // radix.cu
 int radix_sort_u64(kssd_ctx *c, uint64_t *d_keys, uint64_t *d_tmp, uint64_t n, int lo_bits_begin, int lo_bits_end,

@@ -15,6 +15,8 @@
 //  * half_k - drlevel > 8 (64-bit hashes, sketch.cpp:336): hashSet64 is filled instead, sorted ascending, and the sparse
 //    .index / .dict list the hashes in ascending order (the reference writes its hash map's iteration order).
 #include <err.h>
+#include <fcntl.h>
+#include <unistd.h>
 #include <omp.h>
 #include <sys/stat.h>
 #include <zlib.h>
@@ -45,7 +47,45 @@ const unsigned char kSeparator = '\n';  // any non-ACGT byte resets the valid-ru
 // threads run in parallel; a batch is submitted once its last writer has finished.
 class BatchFiller {
   public:
-    BatchFiller(kssd_ctx *ctx, bool has_qual) : ctx_(ctx), has_qual_(has_qual) {}
+    BatchFiller(kssd_ctx *ctx, bool has_qual, bool raw = false) : ctx_(ctx), has_qual_(has_qual), raw_(raw) {}
+
+    // RAW FASTA text (kssd_batch.raw_fasta, tokenised on the device): reserves a piece of prefix_len + n bytes (padded with
+    // '\n' to a multiple of 32), copies the prefix and lets `fill` put the n text bytes in place -- outside the lock.
+    template <typename Fill>
+    void append_raw(uint32_t genome, const unsigned char *prefix, size_t prefix_len, size_t n, int flags, Fill &&fill) {
+        const size_t need = (prefix_len + n + 31) & ~(size_t)31;
+        kssd_batch *b;
+        size_t at;
+        {
+            std::unique_lock<std::mutex> lock(mu_);
+            if (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
+            if (!cur_) {
+                check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, need), 1 << 16), "batch_acquire");
+                cur_->n_bytes = 0;
+                cur_->n_seg = 0;
+                cur_->first_emit = 0;
+                cur_->raw_fasta = 1;
+            }
+            b = cur_;
+            at = b->n_bytes;
+            b->seg_off[b->n_seg] = at;
+            b->seg_genome[b->n_seg] = genome;
+            b->seg_flags[b->n_seg] = (uint8_t)flags;
+            b->seg_first[b->n_seg] = (uint32_t)prefix_len;
+            b->n_seg++;
+            b->n_bytes += need;
+            b->seg_off[b->n_seg] = b->n_bytes;
+            writers_++;
+        }
+        if (prefix_len) memcpy(b->seq + at, prefix, prefix_len);
+        fill(b->seq + at + prefix_len);
+        memset(b->seq + at + prefix_len + n, '\n', need - prefix_len - n);
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            writers_--;
+        }
+        cv_.notify_all();
+    }
 
     // seq[0, n) (+ qual) of `genome`; when `terminate` one separator byte is appended after the bytes
     void append(uint32_t genome, const unsigned char *seq, const unsigned char *qual, size_t n, bool terminate) {
@@ -101,17 +141,138 @@ class BatchFiller {
         cur_ = nullptr;
     }
     kssd_ctx *ctx_;
-    bool has_qual_;
+    bool has_qual_, raw_;
     std::mutex mu_;
     std::condition_variable cv_;
     int writers_ = 0;  // slices reserved in cur_ whose copy has not finished
     kssd_batch *cur_ = nullptr;
 };
 
+// ---- plain FASTA files: the text goes to the GPU as it is ----------------------------------------
+// The host only reads bytes: a file is cut into pieces of kRawPiece bytes, each read straight into the pinned batch, and the
+// device strips headers and line ends (fasta.cu).  What the host keeps per file is the line state at the cut (inside a header
+// line / at a line start / inside a sequence line) and the last kCtx sequence bytes of the running record, which prefix the
+// next piece so that k-mers across the cut are seen (kssd_batch.raw_fasta).  One thread reads one file front to back -- a
+// 3 Gbp genome moves at memory-copy speed instead of through kseq's byte loop (the reference uses RabbitFX's chunked
+// reader for such files, src/sketch.cpp:173-238, :380-450).
+inline bool is_hdr_char(unsigned char c) { return c == '>' || c == '@'; }
+
+struct RawSlicer {
+    static constexpr int kCtx = 31;  // >= 2 * half_k - 1 for half_k <= 16
+    bool hdr = false;     // the line that holds the next byte is a header line
+    bool at_ls = true;    // the next byte is the first of a line
+    unsigned char ctx[kCtx];
+    int n_ctx = 0;
+
+    // prefix + flags of the piece that starts at the current position (file offset > 0)
+    int next_prefix(unsigned char *out, size_t &len) const {
+        len = 0;
+        if (hdr && !at_ls) return KSSD_SEG_IN_HEADER;
+        if (n_ctx == 0) return at_ls ? 0 : KSSD_SEG_MID_LINE;
+        memcpy(out, ctx, n_ctx);
+        len = n_ctx;
+        if (at_ls) out[len++] = '\n';
+        return KSSD_SEG_MID_LINE;
+    }
+
+    void push(unsigned char c) {
+        if (n_ctx == kCtx) memmove(ctx, ctx + 1, --n_ctx);
+        ctx[n_ctx++] = c;
+    }
+
+    // advance over the piece p[0, n) that was just read; `next` = the byte after it (or '\n' at the end of the file).
+    // Only the tail matters: find, walking back line by line with memrchr (long lines cost nothing), a position from which
+    // a forward replay gives the state at the end -- a header line (nothing before it matters), a line start with > kCtx
+    // bytes after it, or the piece start with the state this object already holds.
+    void advance(const unsigned char *p, size_t n, unsigned char next) {
+        size_t from = 0;
+        bool fresh = false;        // replay from `from` with an empty context instead of the current state
+        bool fresh_at_ls = false;  // ... `from` is a line start (else: inside a sequence line, or at the '\n' that ends a header line)
+        bool fresh_hdr = false;
+        size_t i = n, kept = 0;
+        while (true) {
+            const unsigned char *nl = i ? (const unsigned char *)memrchr(p, '\n', i) : nullptr;
+            if (!nl) {  // p[0, i) belongs to the line the piece started in (or, at_ls, to a line that starts at p[0])
+                const bool first_is_hdr = at_ls ? (n > 0 && is_hdr_char(p[0])) : hdr;
+                if (first_is_hdr && i < n) { from = i; fresh = true; fresh_hdr = true; }                     // p[i] is the '\n' that ends it
+                else if (!first_is_hdr && kept + i > (size_t)kCtx + 1 && i > (size_t)kCtx + 2) { from = i - (kCtx + 2); fresh = true; }
+                break;  // else: replay the whole piece from the current state
+            }
+            const size_t ls = (size_t)(nl - p) + 1;
+            if (ls < i && is_hdr_char(p[ls])) { from = ls; fresh = true; fresh_at_ls = true; break; }
+            kept += i - ls;
+            if (kept > (size_t)kCtx + 1) { from = ls; fresh = true; fresh_at_ls = true; break; }
+            i = ls - 1;
+        }
+        if (fresh) {
+            n_ctx = 0;
+            at_ls = fresh_at_ls;
+            hdr = fresh_hdr;
+        }
+        for (size_t j = from; j < n; j++) {
+            const unsigned char c = p[j];
+            if (at_ls) {
+                hdr = is_hdr_char(c);
+                at_ls = false;
+                if (hdr) n_ctx = 0;
+            }
+            if (c == '\n') at_ls = true;
+            else if (!hdr && !(c == '\r' && (j + 1 < n ? p[j + 1] : next) == '\n')) push(c);
+        }
+    }
+};
+
+size_t raw_piece_bytes() {
+    const char *e = getenv("KSSD_B200_RAW_PIECE_BYTES");  // tests cut small files into many pieces
+    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(64u << 20);
+    return std::max<size_t>(v, 64);
+}
+
+// plain FASTA = not gzip (magic 1f 8b) and the first byte is '>' (kseq skips anything before the first '>' / '@': such files
+// and FASTQ go through kseq)
+bool looks_like_plain_fasta(int fd) {
+    unsigned char b[2] = {0, 0};
+    return pread(fd, b, 2, 0) >= 1 && b[0] == '>';
+}
+
+// -> false on a read error (the caller falls back to kseq for the whole job)
+bool read_raw_fasta(int fd, uint64_t size, uint32_t genome, BatchFiller &filler) {
+    const size_t piece = raw_piece_bytes();
+    RawSlicer sl;
+    uint64_t pos = 0;
+    bool ok = true;
+    while (pos < size && ok) {
+        uint64_t end = std::min<uint64_t>(size, pos + piece);
+        if (end < size) {  // a piece must not end with the '\r' of a "\r\n"
+            unsigned char last = 0;
+            if (pread(fd, &last, 1, (off_t)(end - 1)) == 1 && last == '\r' && end - 1 > pos) end--;
+        }
+        unsigned char prefix[RawSlicer::kCtx + 1];
+        size_t plen = 0;
+        const int flags = pos == 0 ? 0 : sl.next_prefix(prefix, plen);
+        const size_t n = (size_t)(end - pos);
+        unsigned char next = '\n';
+        if (end < size && pread(fd, &next, 1, (off_t)end) != 1) next = '\n';
+        filler.append_raw(genome, prefix, plen, n, flags, [&](unsigned char *dst) {
+            size_t got = 0;
+            while (got < n) {
+                const ssize_t r = pread(fd, dst + got, n - got, (off_t)(pos + got));
+                if (r <= 0) { ok = false; memset(dst + got, '\n', n - got); break; }
+                got += (size_t)r;
+            }
+            if (end < size) sl.advance(dst, n, next);
+        });
+        pos = end;
+    }
+    return ok;
+}
+
 bool by_size_desc(const fileInfo_t &a, const fileInfo_t &b) { return a.fileSize > b.fileSize; }  // cmpFile, sketch.cpp:39
 
 bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, const kssd_parameter_t &p, bool fastq,
-                  int leastQual, int leastNumKmer, std::vector<sketch_t> &sketches, sketchInfo_t &info, std::string outputFile) {
+                  int leastQual, int leastNumKmer, std::vector<sketch_t> &sketches, sketchInfo_t &info, std::string outputFile,
+                  bool allow_raw = true) {
+    if (getenv("KSSD_B200_NO_RAW_FASTA")) allow_raw = false;
     const bool use64 = p.half_k - p.drlevel > 8;  // sketch.cpp:336
     // file list: as sketch.cpp:348-374 (stat every file, sort by size descending)
     std::ifstream fs(inputFile);
@@ -140,12 +301,28 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         check(kssd_b200_set_params(ctxs[g], p.half_k, p.half_subk, p.drlevel, p.shuffled_dim), "set_params");
         check(kssd_b200_sketch_begin(ctxs[g], (uint32_t)n, fastq ? 1 : 0, leastQual, leastNumKmer), "sketch_begin");
     }
-    std::vector<BatchFiller *> fillers(G);
-    for (size_t g = 0; g < G; g++) fillers[g] = new BatchFiller(ctxs[g], fastq);
+    std::vector<BatchFiller *> fillers(G), raw_fillers(G);
+    for (size_t g = 0; g < G; g++) {
+        fillers[g] = new BatchFiller(ctxs[g], fastq);
+        raw_fillers[g] = new BatchFiller(ctxs[g], false, true);
+    }
+    bool raw_failed = false;
 
     if (numThreads < 1) numThreads = 1;
 #pragma omp parallel for num_threads(numThreads) schedule(dynamic)
     for (size_t t = 0; t < n; t++) {
+        if (allow_raw && !fastq) {  // plain FASTA text: straight to the GPU, tokenised there (fasta.cu)
+            const int fd = open(fileList[t].fileName.c_str(), O_RDONLY);
+            if (fd < 0) err(errno, "cannot open the genome file: %s\n", fileList[t].fileName.c_str());
+            struct stat st;
+            const bool plain = fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0 && looks_like_plain_fasta(fd);
+            if (plain && !read_raw_fasta(fd, (uint64_t)st.st_size, (uint32_t)t, *raw_fillers[t % G])) {
+#pragma omp atomic write
+                raw_failed = true;
+            }
+            close(fd);
+            if (plain) continue;
+        }
         gzFile fp = gzopen(fileList[t].fileName.c_str(), "r");
         if (fp == NULL) err(errno, "cannot open the genome file: %s\n", fileList[t].fileName.c_str());
         gzbuffer(fp, 1 << 20);
@@ -187,12 +364,20 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
 
     std::vector<const uint32_t *> hashes(G, nullptr);
     std::vector<const uint64_t *> hashes64(G, nullptr), off(G, nullptr);
+    std::vector<int> rcs(G, KSSD_OK);
 #pragma omp parallel for num_threads((int)G) schedule(static, 1)
     for (size_t g = 0; g < G; g++) {
         fillers[g]->flush();
-        if (use64) check(kssd_b200_sketch_finish64(ctxs[g], &hashes64[g], &off[g]), "sketch_finish64");
-        else check(kssd_b200_sketch_finish(ctxs[g], &hashes[g], &off[g]), "sketch_finish");
+        raw_fillers[g]->flush();
+        rcs[g] = use64 ? kssd_b200_sketch_finish64(ctxs[g], &hashes64[g], &off[g]) : kssd_b200_sketch_finish(ctxs[g], &hashes[g], &off[g]);
+        if (rcs[g] != KSSD_OK && rcs[g] != KSSD_E_SYNTAX) check(rcs[g], "sketch_finish");
         delete fillers[g];
+        delete raw_fillers[g];
+    }
+    for (size_t g = 0; g < G; g++) raw_failed |= rcs[g] == KSSD_E_SYNTAX;
+    if (raw_failed) {  // text that is not plain FASTA (or a read error): the host parser decides, as in the reference
+        std::cerr << "-----raw FASTA text was not accepted by the device tokeniser, parsing all files with kseq" << std::endl;
+        return sketch_files(inputFile, isQuery, numThreads, p, fastq, leastQual, leastNumKmer, sketches, info, outputFile, false);
     }
     sketches.reserve(sketches.size() + n);
     for (size_t t = 0; t < n; t++) {

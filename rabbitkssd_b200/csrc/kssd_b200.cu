@@ -5,5 +5,6 @@
 #include "segsort.cu"
 #include "index.cu"
 #include "hash64.cu"
+#include "fasta.cu"
 #include "dist.cu"
 #include "capi.cu"

@@ -45,6 +45,7 @@ struct ScanArgs {
     uint32_t *emit_gen;        // 64-bit hash configuration (half_k - drlevel > 8, src/sketch.cpp:336): genome of emit[i]; else null
     const uint64_t *seg_off;   // segment table of the buffer (coordinates: byte 0 of this launch = pos_base)
     const uint32_t *seg_genome;
+    const uint64_t *seg_first; // optional, per segment: k-mers ending before this position (coordinates of seg_off) are context only
     uint32_t n_seg;
     uint64_t pos_base;
     unsigned long long *cursor;
@@ -336,6 +337,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             p = ver_pos[base + lane];
             ok = verify_kmer(a, p, hash);
         }
+        auto segment_of = [&](uint64_t gpos) {  // owning segment: largest s with seg_off[s] <= pos
+            uint32_t lo = 0, hi = a.n_seg;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
+            }
+            return lo;
+        };
+        uint32_t seg = 0;
+        if (a.seg_first && ok) {  // raw-text batches: a piece may begin with context that an earlier piece already scanned
+            seg = segment_of(a.pos_base + p);
+            ok = a.pos_base + p >= __ldg(a.seg_first + seg);
+        }
         const uint32_t m = __ballot_sync(FULL, ok);
         if (m) {
             unsigned long long at = 0;
@@ -343,13 +357,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) kssd_scan_kernel(const __grid
             at = __shfl_sync(FULL, at, 0) + __popc(m & lt);
             uint32_t genome = 0xFFFFFFFFu;  // lanes without a key to store
             if (ok && at < a.emit_cap) {
-                const uint64_t gpos = a.pos_base + p;
-                uint32_t lo = 0, hi = a.n_seg;  // owning segment: largest s with seg_off[s] <= pos
-                while (hi - lo > 1) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    if (__ldg(a.seg_off + mid) <= gpos) lo = mid; else hi = mid;
-                }
-                genome = __ldg(a.seg_genome + lo);
+                if (!a.seg_first) seg = segment_of(a.pos_base + p);
+                genome = __ldg(a.seg_genome + seg);
                 if (a.emit_gen) {
                     a.emit[at] = hash;
                     a.emit_gen[at] = genome;
@@ -574,7 +583,7 @@ static int launch_w0(kssd_ctx *c, const ScanArgs &a, size_t smem, int w0, bool a
 
 int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64_t n_bytes,
                 const uint64_t *d_seg_off, const uint32_t *d_seg_genome, uint32_t n_seg, uint64_t first_emit,
-                uint64_t pos_base) {
+                uint64_t pos_base, const uint64_t *d_seg_first) {
     if (n_bytes == 0 || n_seg == 0) return KSSD_OK;
     if ((reinterpret_cast<uintptr_t>(d_seq) & 15) || (d_qual && (reinterpret_cast<uintptr_t>(d_qual) & 15))) {
         set_error("sequence / quality device buffers must be 16-byte aligned");
@@ -601,6 +610,7 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
     a.emit_gen = c->hash64 ? c->d_emit_gen.as<uint32_t>() : nullptr;
     a.seg_off = d_seg_off;
     a.seg_genome = d_seg_genome;
+    a.seg_first = d_seg_first;
     a.n_seg = n_seg;
     a.cursor = c->d_cursor.as<unsigned long long>();
     a.gcount = c->d_gcount.as<uint32_t>();

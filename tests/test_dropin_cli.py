@@ -316,3 +316,52 @@ def test_multi_gpu_cli_equals_reference(work):
         _run(REF, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, rdir)
         _run_env(NEW, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_MIN_ROWS_PER_GPU": "2"})
         assert sorted(formats.parse_dist_text(os.path.join(rdir, "m.dist"))) == sorted(formats.parse_dist_text(os.path.join(ndir, "m.dist")))
+
+
+def test_raw_fasta_text_path_equals_reference(work, tmp_path):
+    """Plain FASTA files go to the GPU as raw text (sliced into pieces by the shim, tokenised by fasta.cu); gzip files and
+    anything that does not start with '>' go through kseq.  Small pieces (KSSD_B200_RAW_PIECE_BYTES) force many cuts; the
+    hash sets must equal the reference's (kseq on the host) for one-line records, CRLF, blank lines, tiny records; a file
+    with a '+' line makes the shim fall back to kseq for the whole job."""
+    import gzip
+    import test_gpu_fasta as tf
+    d = work["d"]
+    texts = tf._texts()
+    texts.append(b">h1\n" + bytes(synth.random_bases(5, 200000)) + b"\nAC\nGT\n>h2 x\nA\n\n\nC\n>h3\n" + bytes(synth.random_bases(6, 90000)) + b"\r\nGG\r\n")
+    files = []
+    for i, t in enumerate(texts):
+        p = str(tmp_path / f"raw{i}.fa")
+        with open(p, "wb") as f:
+            f.write(t)
+        files.append(p)
+    gz = str(tmp_path / "z.fa.gz")
+    with gzip.open(gz, "wb") as f:
+        f.write(texts[0])
+    files.append(gz)
+    lst = str(tmp_path / "raw.list")
+    with open(lst, "w") as f:
+        f.write("\n".join(files) + "\n")
+    shuf = os.path.join(d, "L3K10.shuf")
+    _run(REF, ["sketch", "-q", "-L", shuf, "-i", lst, "-o", "rawref", "-t", "3"], work["dirs"]["ref"])
+    want = _sketch_sets(os.path.join(work["dirs"]["ref"], "rawref.sketch"))
+    for env in ({}, {"KSSD_B200_RAW_PIECE_BYTES": "4099"}, {"KSSD_B200_RAW_PIECE_BYTES": "70001"}, {"KSSD_B200_NO_RAW_FASTA": "1"}):
+        out = _run_env(NEW, ["sketch", "-q", "-L", shuf, "-i", lst, "-o", "rawnew", "-t", "3"], work["dirs"]["new"], env)
+        got = _sketch_sets(os.path.join(work["dirs"]["new"], "rawnew.sketch"))
+        assert sorted(got) == sorted(want), env
+        for n in want:
+            assert np.array_equal(got[n], want[n]), (env, n)
+        assert "parsing all files with kseq" not in out
+    # '+' line: not plain FASTA
+    bad = str(tmp_path / "bad.fa")
+    t = texts[0]
+    cut = t.find(b"\n", 3000) + 1
+    with open(bad, "wb") as f:
+        f.write(t[:cut] + b"+\n" + t[cut:])
+    with open(lst, "a") as f:
+        f.write(bad + "\n")
+    _run(REF, ["sketch", "-q", "-L", shuf, "-i", lst, "-o", "rawref2", "-t", "3"], work["dirs"]["ref"])
+    out = _run(NEW, ["sketch", "-q", "-L", shuf, "-i", lst, "-o", "rawnew2", "-t", "3"], work["dirs"]["new"])
+    assert "parsing all files with kseq" in out
+    want = _sketch_sets(os.path.join(work["dirs"]["ref"], "rawref2.sketch"))
+    got = _sketch_sets(os.path.join(work["dirs"]["new"], "rawnew2.sketch"))
+    assert sorted(got) == sorted(want) and all(np.array_equal(got[n], want[n]) for n in want)
