@@ -143,9 +143,13 @@ def test_sliced_files(ctx, piece):
     pieces = []
     for g, t in enumerate(texts):
         pieces += slice_pieces(g, t, piece + 13 * g)
+    # long header lines and blank-line runs, so that cuts also fall inside a header line and right at a line start after one
+    extra = b"".join(b">" + b"h" * (3000 + 700 * j) + b"\n" + bytes(synth.random_bases(70 + j, 2500)) + b"\n\n" for j in range(12))
+    texts.append(extra)
+    want = _expect(10, 6, 3, texts)
+    pieces += slice_pieces(len(texts) - 1, extra, min(piece, 4099))
     assert any(p[2] == 2 and p[3] for p in pieces)
-    if piece < 5000:
-        assert any(p[2] == 1 for p in pieces) and any(p[2] == 0 and i for i, p in enumerate(pieces))
+    assert any(p[2] == 1 for p in pieces)
     order = np.random.default_rng(piece).permutation(len(pieces))  # pieces are independent of each other
     batches = [[pieces[i] for i in order[a:a + 50]] for a in range(0, len(order), 50)]
     got = _run(ctx, 10, 6, 3, len(texts), batches)

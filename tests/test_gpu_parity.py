@@ -58,7 +58,7 @@ def test_index_and_distances_equal_reference_golden(ctx, case):
         assert uh.dtype == np.uint64 and np.all(np.diff(uh.astype(np.float64)) > 0)
         want, start = {}, 0
         for hv, cnt in zip(z["index_hash"], z["index_count"]):
-            want[int(hv)] = [int(x) for x in z["dict"][start:start + cnt]]
+            want[int(hv)] = sorted(int(x) for x in z["dict"][start:start + cnt])  # fixture ids are in `names` order, lists in the reference's push order
             start += cnt
         got, start = {}, 0
         for hv, cnt in zip(uh, uc):
@@ -417,7 +417,7 @@ def test_64bit_hashes_equal_oracle_random(ctx):
             assert np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1)), (k, tri, D)
         # the reference's files hold the lists in hash-map order: load them shuffled
         perm = np.random.default_rng(5).permutation(len(uh))
-        starts = np.concatenate([[0], np.cumsum(uc)])
+        starts = np.concatenate([[0], np.cumsum(uc.astype(np.int64))]).astype(np.int64)
         shuffled = np.concatenate([dict_[starts[u]:starts[u + 1]] for u in perm]) if len(perm) else dict_
         ctx.index_load64(uh[perm], uc[perm], shuffled, sizes.astype(np.uint32))
         hits = ctx.dist_rows(h, goff, True, 2 * k, 0.2)
