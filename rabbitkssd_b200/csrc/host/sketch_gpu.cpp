@@ -227,10 +227,19 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     const size_t n = fileList.size();
     std::cerr << "the total fileNumber is: " << n << std::endl;
 
+    const bool trace = getenv("KSSD_B200_TRACE") != nullptr;  // phase times of the shim on stderr
+    double tr0 = get_sec();
+    auto lap = [&](const char *what) {
+        if (!trace) return;
+        const double t = get_sec();
+        std::cerr << "[kssd_b200 trace] " << what << ": " << t - tr0 << " s" << std::endl;
+        tr0 = t;
+    };
     // one context per GPU; file t (position in the size-descending list) goes to GPU t % G, which balances the bytes
     const size_t G = std::max<size_t>(1, std::min(kssd_host::device_count(), n));
     std::vector<kssd_ctx *> ctxs(G);
     for (size_t g = 0; g < G; g++) ctxs[g] = kssd_host::context_at(g);
+    lap("contexts");
 #pragma omp parallel for num_threads((int)G) schedule(static, 1)
     for (size_t g = 0; g < G; g++) {  // the table build walks all 16^half_subk entries: one host thread per context
         check(kssd_b200_set_params(ctxs[g], p.half_k, p.half_subk, p.drlevel, p.shuffled_dim), "set_params");
@@ -242,6 +251,7 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         raw_fillers[g] = new BatchFiller(ctxs[g], false, true);
     }
     bool raw_failed = false;
+    lap("set_params + sketch_begin");
 
     if (numThreads < 1) numThreads = 1;
 #pragma omp parallel for num_threads(numThreads) schedule(dynamic)
@@ -297,6 +307,7 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         gzclose(fp);
     }
 
+    lap("read / parse files into batches");
     std::vector<const uint32_t *> hashes(G, nullptr);
     std::vector<const uint64_t *> hashes64(G, nullptr), off(G, nullptr);
     std::vector<int> rcs(G, KSSD_OK);
@@ -314,6 +325,7 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         std::cerr << "-----raw FASTA text was not accepted by the device tokeniser, parsing all files with kseq" << std::endl;
         return sketch_files(inputFile, isQuery, numThreads, p, fastq, leastQual, leastNumKmer, sketches, info, outputFile, false);
     }
+    lap("flush + sketch_finish");
     sketches.reserve(sketches.size() + n);
     for (size_t t = 0; t < n; t++) {
         const size_t g = t % G;
@@ -332,7 +344,9 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     info.drlevel = p.drlevel;
     info.id = (p.half_k << 8) + (p.half_subk << 4) + p.drlevel;
     info.genomeNumber = sketches.size();
+    lap("sketch_t vectors");
     saveSketches(sketches, info, outputFile);
+    lap("saveSketches");
     std::cerr << "save the sketches into: " << outputFile << std::endl;
     if (!isQuery) {
         const double t0 = get_sec();
