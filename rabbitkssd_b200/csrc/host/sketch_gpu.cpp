@@ -132,7 +132,7 @@ class BatchFiller {
         if (cur_) submit(lock);
     }
 
-    static constexpr size_t kBatchBytes = 256u << 20;  // pinned batch size
+    static constexpr size_t kBatchBytes = 64u << 20;   // pinned batch size: small enough that the first copy starts early and page-locking is cheap
     static constexpr size_t kPieceBytes = 8u << 20;    // small records are gathered per thread up to this much
     static constexpr size_t kDirectBytes = 1u << 20;   // records at least this long go straight from the parser's buffer
 
@@ -159,7 +159,7 @@ class BatchFiller {
 // reader for such files, src/sketch.cpp:173-238, :380-450).
 size_t raw_piece_bytes() {
     const char *e = getenv("KSSD_B200_RAW_PIECE_BYTES");  // tests cut small files into many pieces
-    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(64u << 20);
+    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(16u << 20);
     return std::max<size_t>(v, 64);
 }
 

@@ -166,20 +166,17 @@ __global__ void __launch_bounds__(256) filter_set_kernel(const uint32_t *__restr
     }
 }
 
-// grid = (genomes, chunks): the genome id is blockIdx.x.  Counts the pairs per bucket and draws each pair's arrival rank
-// inside its bucket (0xFFFFFFFF: the pair is not indexed).
-__global__ void __launch_bounds__(128) bucket_hist_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, int shift,
-                                                          uint32_t last_bucket, uint32_t h_lo, uint32_t h_last, const PostingFilter f,
+// One thread per hash (the sketches are genome-major, so "genomes >= g_begin" is "elements >= genome_off[g_begin]").
+// Counts the pairs per bucket and draws each pair's arrival rank inside its bucket (0xFFFFFFFF: the pair is not indexed).
+__global__ void __launch_bounds__(256) bucket_hist_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, uint64_t total,
+                                                          int shift, uint32_t last_bucket, uint32_t h_lo, uint32_t h_last, const PostingFilter f,
                                                           uint32_t *__restrict__ bcount, uint32_t *__restrict__ rank) {
-    const uint32_t g = blockIdx.x;
-    if (g < f.g_begin) return;
-    const uint64_t e1 = genome_off[g + 1];
-    for (uint64_t e = genome_off[g] + (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; e < e1; e += (uint64_t)gridDim.y * blockDim.x) {
-        const uint32_t h = hashes[e];
-        uint32_t r = 0xFFFFFFFFu;
-        if (h >= h_lo && h <= h_last && filter_pass(f, h)) r = atomicAdd(bcount + min((h - h_lo) >> shift, last_bucket), 1u);  // arrival order
-        rank[e] = r;
-    }
+    const uint64_t i = (f.g_begin ? genome_off[f.g_begin] : 0) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const uint32_t h = hashes[i];
+    uint32_t r = 0xFFFFFFFFu;
+    if (h >= h_lo && h <= h_last && filter_pass(f, h)) r = atomicAdd(bcount + min((h - h_lo) >> shift, last_bucket), 1u);  // arrival order
+    rank[i] = r;
 }
 
 // the slot inside the bucket was drawn by the histogram pass
@@ -296,8 +293,9 @@ static int index_build_bucketed(kssd_ctx *c, const uint32_t *d_hashes, const uin
     uint32_t *tmp_rel = tmp_hash + total;
     const uint64_t avg_len = total / n_genomes + 1;
     const uint32_t chunks = (uint32_t)std::min<uint64_t>(64, (avg_len + 255) / 256);
-    bucket_hist_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, h_last, filter, bcount,
-                                                                tmp_hash /* rank, dead before the sort */);
+    // (a restricted build launches threads for all hashes; those past the end after the g_begin offset exit at once)
+    bucket_hist_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_hashes, d_genome_off, total, shift, nb - 1, h_lo, h_last, filter, bcount,
+                                                                       tmp_hash /* rank, dead before the sort */);
     segment_scan_kernel<<<1, 1024, 0, st>>>(bcount, nb, bstart, nullptr);
     bucket_deal_kernel<<<dim3(n_genomes, chunks), 128, 0, st>>>(d_hashes, d_genome_off, shift, nb - 1, h_lo, filter.g_begin, bstart, tmp_hash,
                                                                 c->d_pairs.as<uint64_t>());
