@@ -568,7 +568,12 @@ int index_build_device(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_
         c->max_ref_size = 0;
     }
     c->n_uniq = n_uniq;
-    KSSD_TRY(index_build_buckets(c, known_max));
+    if (restricted) {  // alldist rows only: the work lists come from a walk over the lists, no hash is ever looked up
+        c->n_buckets = 0;
+        c->bucket_shift = 0;
+    } else {
+        KSSD_TRY(index_build_buckets(c, known_max));
+    }
     c->have_index = true;
     return KSSD_OK;
 }
