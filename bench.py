@@ -289,6 +289,8 @@ def run_b200(args):
     numa = bind_to_gpu_numa(local_rank)
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # NCCL would print its version on stdout, next to the JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_total, length, family = args.genomes, args.genome_len, args.family
     assert n_total % (world * family) == 0, "genomes must divide evenly into families per rank"

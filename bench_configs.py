@@ -38,6 +38,8 @@ def _setup(args):
     numa = B.bind_to_gpu_numa(local_rank)
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from rabbitkssd_b200 import api
     ctx = api.Context(local_rank)

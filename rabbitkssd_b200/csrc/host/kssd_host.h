@@ -32,8 +32,10 @@ inline void check(int rc, const char *what) {
 
 // The reference reports errors with a message on stderr and exit(1) (e.g. src/dist.cpp:41-43); the shims do the same with
 // the library's text.
-inline const std::vector<int> &device_ids() {
+inline const std::vector<int> &device_ids(bool fatal = true) {
     static std::vector<int> ids;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
     if (!ids.empty()) return ids;
     const char *many = getenv("KSSD_B200_DEVICES");
     const char *one = getenv("KSSD_B200_DEVICE");
@@ -42,7 +44,10 @@ inline const std::vector<int> &device_ids() {
         return ids;
     }
     int n = 0;
-    check(kssd_b200_device_count(&n), "libkssd_b200");
+    if (kssd_b200_device_count(&n) != KSSD_OK) {
+        if (fatal) check(KSSD_E_CUDA, "libkssd_b200");
+        return ids;  // empty: no usable device (early, non-fatal probe)
+    }
     if (many && *many && strcmp(many, "all")) {
         for (const char *p = many; *p;) {
             char *end = nullptr;
@@ -58,23 +63,41 @@ inline const std::vector<int> &device_ids() {
 }
 inline size_t device_count() { return device_ids().size(); }
 // contexts are created on first use: a job that needs one GPU initialises one
-inline kssd_ctx *context_at(size_t i) {
+inline kssd_ctx *context_at(size_t i, bool fatal = true) {
     static std::mutex mu;
     static std::vector<kssd_ctx *> pool;
+    const std::vector<int> &ids = device_ids(fatal);
     std::lock_guard<std::mutex> lock(mu);
-    const std::vector<int> &ids = device_ids();
     if (pool.size() < ids.size()) pool.resize(ids.size(), nullptr);
     if (i >= pool.size()) {
+        if (!fatal) return nullptr;
         fprintf(stderr, "ERROR: libkssd_b200: device slot %zu of %zu\n", i, pool.size());
         exit(1);
     }
     if (!pool[i] && kssd_b200_init(&pool[i], ids[i]) != KSSD_OK) {
+        pool[i] = nullptr;
+        if (!fatal) return nullptr;
         fprintf(stderr, "ERROR: libkssd_b200: %s\n", kssd_b200_last_error());
         exit(1);
     }
     return pool[i];
 }
 inline kssd_ctx *context() { return context_at(0); }
+
+// CUDA context creation takes ~0.9 s on a B200 box -- as long as sketching a thousand bacterial genomes.  The shims start it
+// on a background thread when the program is loaded (a static object in sketch_gpu.cpp), so that it overlaps with argument
+// parsing, the read of the .shuf file and the stat() of the input list; context_at() then finds the context ready or waits
+// for the same mutex.  KSSD_B200_LAZY_INIT=1 turns it off (e.g. `rabbit_kssd info`, which never needs a GPU, then pays nothing).
+struct EarlyInit {
+    std::thread t;
+    EarlyInit() {
+        if (getenv("KSSD_B200_LAZY_INIT")) return;
+        t = std::thread([] { context_at(0, false); });  // a host without a GPU still runs shuffle / info / convert
+    }
+    ~EarlyInit() {
+        if (t.joinable()) t.join();
+    }
+};
 
 // ---- what transSketches left behind ------------------------------------------------------------
 // `alldist -i <genome list>` and `dist -r <genome list>` run sketch -> transSketches -> index_tridist / index_dist in ONE

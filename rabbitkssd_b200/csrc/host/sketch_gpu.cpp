@@ -37,6 +37,9 @@
 // src/sketch.cpp:17 instantiates the same static kseq functions in its own translation unit
 KSEQ_INIT(gzFile, gzread)
 
+// one per program: starts creating the CUDA context of the first GPU while main() is still parsing its arguments
+static kssd_host::EarlyInit g_early_init;
+
 namespace {
 
 using kssd_host::check;
