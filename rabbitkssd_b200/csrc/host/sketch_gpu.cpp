@@ -61,6 +61,7 @@ class BatchFiller {
         const size_t need = (prefix_len + n + 31) & ~(size_t)31;
         kssd_batch *b;
         size_t at;
+        const double t_in = get_sec();
         {
             std::unique_lock<std::mutex> lock(mu_);
             if (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
@@ -82,12 +83,16 @@ class BatchFiller {
             b->seg_off[b->n_seg] = b->n_bytes;
             writers_++;
         }
+        const double t_got = get_sec();
         if (prefix_len) memcpy(b->seq + at, prefix, prefix_len);
         fill(b->seq + at + prefix_len);
         memset(b->seq + at + prefix_len + n, '\n', need - prefix_len - n);
+        const double t_filled = get_sec();
         {
             std::lock_guard<std::mutex> lock(mu_);
             writers_--;
+            t_reserve_ += t_got - t_in;
+            t_fill_ += t_filled - t_got;
         }
         cv_.notify_all();
     }
@@ -133,6 +138,9 @@ class BatchFiller {
     void flush() {
         std::unique_lock<std::mutex> lock(mu_);
         if (cur_) submit(lock);
+        if (getenv("KSSD_B200_TRACE") && (t_fill_ > 0 || t_submit_ > 0))
+            std::cerr << "[kssd_b200 trace] filler(" << (raw_ ? "raw" : "parsed") << "): thread-seconds waiting to reserve " << t_reserve_ << ", copying " << t_fill_
+                      << "; submits " << n_submit_ << " took " << t_submit_ << " s, of which waiting for writers " << t_drain_ << std::endl;
     }
 
     static constexpr size_t kBatchBytes = 64u << 20;   // pinned batch size: small enough that the first copy starts early and page-locking is cheap
@@ -141,10 +149,17 @@ class BatchFiller {
 
   private:
     void submit(std::unique_lock<std::mutex> &lock) {  // all slices of cur_ are reserved by now: wait for their copies
+        const double t0 = get_sec();
         cv_.wait(lock, [&] { return writers_ == 0; });
+        const double t1 = get_sec();
         if (cur_->n_bytes) check(kssd_b200_batch_submit(ctx_, cur_), "batch_submit");
         cur_ = nullptr;
+        t_drain_ += t1 - t0;
+        t_submit_ += get_sec() - t0;
+        n_submit_++;
     }
+    double t_reserve_ = 0, t_fill_ = 0, t_submit_ = 0, t_drain_ = 0;
+    int n_submit_ = 0;
     kssd_ctx *ctx_;
     bool has_qual_, raw_;
     std::mutex mu_;
