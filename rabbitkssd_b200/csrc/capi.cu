@@ -190,6 +190,8 @@ void kssd_b200_destroy(kssd_ctx *c) {
         c->d_stage_cseg[i].release();
     }
     c->d_fa_scratch.release();
+    c->d_tile_rows.release();
+    c->h_tile_rows.release();
     c->d_filter.release();
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);

@@ -189,6 +189,10 @@ struct kssd_ctx {
     kssd::DevBuf d_q_list_begin;  // alldist: posting ranges per row (uint2 begin, end), slots of row g at q_off[g]
     kssd::DevBuf d_q_list_end;    // alldist: ranges filled per row
     kssd::HostBuf h_hits;
+    kssd::DevBuf d_tile_rows;     // alldist: first row of every tile of the packed triangle (dist.cu)
+    kssd::HostBuf h_tile_rows;
+    uint64_t tile_key[4] = {0, 0, 0, 0};
+    uint32_t n_tile_rows = 0;
 
     kssd::TimedLaunches t_scan, t_count;
 };

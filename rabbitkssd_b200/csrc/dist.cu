@@ -23,6 +23,7 @@
 //  The device test is conservative (superset); the host recomputes with the reference's exact expressions.
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 
 #include "common.cuh"
 #include "smem_sort.cuh"
@@ -37,35 +38,52 @@ static constexpr int kDistThreads = 512;
 // work[q_off[g] + i], i < fill[g - row_begin]: the ranges row g streams.  A row has at most |sketch(g)| ranges (one
 // per hash), so the slots of row g start at q_off[g]; more than that means the query sketches are not the indexed
 // ones (flags[0]).
+// A warp takes 32 lists at a time and spreads their postings -- not the lists -- over its lanes: every posting but the last
+// of a list is one emit, the emits of the 32 lists are numbered by a warp prefix sum and lane l takes emits l, l + 32, ...
+// (the list of an emit is found by a 5-step search over the prefix sums held by the lanes).  All lanes thus run independent
+// dict -> q_off -> atomic -> store chains, whatever the mix of singleton, short and thousand-member lists.
 __global__ void __launch_bounds__(256) row_work_kernel(const uint64_t *__restrict__ uniq_off, uint64_t n_uniq, const uint32_t *__restrict__ dict,
                                                        const uint64_t *__restrict__ q_off, uint32_t row_begin, uint32_t row_end,
                                                        uint32_t *__restrict__ fill, uint2 *__restrict__ work, uint32_t *__restrict__ flags) {
+    constexpr unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    auto emit = [&](uint32_t p, uint32_t e) {  // posting p of a list that ends at e
-        const uint32_t g = dict[p];
-        if (g < row_begin || g >= row_end) return;
-        const uint64_t o = q_off[g];
-        const uint32_t room = (uint32_t)(q_off[g + 1] - o);
-        const uint32_t slot = atomicAdd(fill + (g - row_begin), 1u);
-        if (slot < room) work[o + slot] = make_uint2(p + 1, e);
-        else atomicExch(flags, 1u);
-    };
     for (uint64_t u0 = warp * 32; u0 < n_uniq; u0 += n_warps * 32) {
         const uint64_t u = u0 + lane;
         uint32_t b = 0, e = 0;
         if (u < n_uniq) { b = (uint32_t)uniq_off[u]; e = (uint32_t)uniq_off[u + 1]; }
-        const uint32_t len = e - b;
-        uint32_t longs = __ballot_sync(0xFFFFFFFFu, len > 2 * kLongList);
-        while (longs) {
-            const int src = __ffs(longs) - 1;
-            longs &= longs - 1;
-            const uint32_t bb = __shfl_sync(0xFFFFFFFFu, b, src), ee = __shfl_sync(0xFFFFFFFFu, e, src);
-            for (uint32_t p = bb + lane; p + 1 < ee; p += 32) emit(p, ee);
+        const uint32_t mine = e > b ? e - b - 1 : 0;  // emits of this lane's list
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += y;
         }
-        if (len <= 2 * kLongList)
-            for (uint32_t p = b; p + 1 < e; p++) emit(p, e);
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        for (uint32_t k0 = 0; k0 < total; k0 += 32) {  // warp-uniform trip count
+            const uint32_t k = k0 + lane;
+            // list of emit k: the first lane j with incl[j] > k
+            int lo = 0;
+#pragma unroll
+            for (int step = 16; step; step >>= 1) {
+                const uint32_t v = __shfl_sync(FULL, incl, lo + step - 1);
+                if (v <= k) lo += step;
+            }
+            const uint32_t jb = __shfl_sync(FULL, b, lo), je = __shfl_sync(FULL, e, lo), jincl = __shfl_sync(FULL, incl, lo);
+            if (k < total) {
+                const uint32_t p = je - 1 - (jincl - k);  // emit t of list j is posting b_j + t; t = k - excl_j, excl_j = incl_j - (e_j - b_j - 1)
+                (void)jb;
+                const uint32_t g = dict[p];
+                if (g >= row_begin && g < row_end) {
+                    const uint64_t o = q_off[g];
+                    const uint32_t room = (uint32_t)(q_off[g + 1] - o);
+                    const uint32_t slot = atomicAdd(fill + (g - row_begin), 1u);
+                    if (slot < room) work[o + slot] = make_uint2(p + 1, je);
+                    else atomicExch(flags, 1u);
+                }
+            }
+        }
     }
 }
 
@@ -87,6 +105,8 @@ struct DistArgs {
     uint32_t n_ref;
     uint32_t tq, tc;             // tile rows, tile cols
     uint32_t n_col_tiles;
+    const uint32_t *tile_rows;   // triangle, one column tile: first row of every tile ([n_tiles] = row_end); a tile then holds only the
+                                 // columns right of its first row, so tiles further down the triangle take more rows.  Else null
     int triangle;
     int containment;
     int zero_pass;               // cells with common == 0 (or an empty sketch) pass the threshold
@@ -154,15 +174,24 @@ __global__ void __launch_bounds__(kDistThreads, 2) dist_tile_kernel(const __grid
     uint16_t *list = reinterpret_cast<uint16_t *>(reinterpret_cast<uint32_t *>(s_raw) + a.list_word_off);
     constexpr unsigned FULL = 0xFFFFFFFFu;
 
-    const uint32_t row_tile = blockIdx.x / a.n_col_tiles;
-    const uint32_t col_tile = blockIdx.x % a.n_col_tiles;
-    const uint32_t r0 = a.row_begin + row_tile * a.tq;
-    const uint32_t r1 = min(r0 + a.tq, a.row_end);
-    const uint32_t c0 = col_tile * a.tc;
-    const uint32_t c1 = min(c0 + a.tc, a.n_ref);
+    uint32_t r0, r1, c0, c1, tc;
+    if (TRI && a.tile_rows) {
+        r0 = a.tile_rows[blockIdx.x];
+        r1 = a.tile_rows[blockIdx.x + 1];
+        c0 = min((r0 + 1) & ~7u, a.n_ref);  // rows stay 16-byte aligned
+        c1 = a.n_ref;
+        tc = max((c1 - c0 + 7) & ~7u, 8u);
+    } else {
+        const uint32_t row_tile = blockIdx.x / a.n_col_tiles;
+        const uint32_t col_tile = blockIdx.x % a.n_col_tiles;
+        r0 = a.row_begin + row_tile * a.tq;
+        r1 = min(r0 + a.tq, a.row_end);
+        c0 = col_tile * a.tc;
+        c1 = min(c0 + a.tc, a.n_ref);
+        tc = a.tc;
+    }
     if (TRI && c1 <= r0 + 1) return;  // whole tile is on or below the diagonal
     const uint32_t n_rows = r1 - r0;
-    const uint32_t tc = a.tc;
     const bool clip = a.n_col_tiles > 1;
     const int lane = threadIdx.x & 31;
     const uint32_t warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
@@ -479,8 +508,33 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     const uint32_t want_tiles = (uint32_t)c->sm_count * 4;
     const uint32_t tq_fill = std::max<uint32_t>(1, rows / want_tiles);
     tq = std::min(tq, tq_fill);
-    const uint32_t n_row_tiles = (rows + tq - 1) / tq;
-    const size_t cnt_smem = ((size_t)tq * tc * cnt_bytes + 15) & ~(size_t)15;
+    uint32_t n_row_tiles = (rows + tq - 1) / tq;
+    // triangle with one column tile: pack the rows by the columns they can still see (src/dist.cpp:207, j > i)
+    const uint32_t *d_tile_rows = nullptr;
+    size_t cnt_smem = ((size_t)tq * tc * cnt_bytes + 15) & ~(size_t)15;
+    if (triangle && n_col_tiles == 1 && rows > 1) {
+        const uint32_t q_max = std::min<uint32_t>(32, std::max<uint32_t>(tq_fill, tq));
+        const uint64_t key[4] = {((uint64_t)row_begin << 32) | row_end, c->n_ref, cap, q_max};
+        if (memcmp(key, c->tile_key, sizeof(key)) != 0 || c->d_tile_rows.p == nullptr) {
+            std::vector<uint32_t> starts;
+            for (uint32_t r = row_begin; r < row_end;) {
+                starts.push_back(r);
+                const uint32_t cc0 = std::min((r + 1) & ~7u, c->n_ref);
+                const uint32_t w = std::max<uint32_t>((c->n_ref - cc0 + 7) & ~7u, 8);
+                r += std::min<uint32_t>(std::max<uint32_t>(cap / w, 1), q_max);
+            }
+            starts.push_back(row_end);
+            KSSD_TRY(c->h_tile_rows.reserve(starts.size() * 4));
+            memcpy(c->h_tile_rows.p, starts.data(), starts.size() * 4);
+            KSSD_TRY(c->d_tile_rows.reserve(starts.size() * 4, st));
+            KSSD_CUDA(cudaMemcpyAsync(c->d_tile_rows.p, c->h_tile_rows.p, starts.size() * 4, cudaMemcpyHostToDevice, st));
+            memcpy(c->tile_key, key, sizeof(key));
+            c->n_tile_rows = (uint32_t)starts.size() - 1;
+        }
+        d_tile_rows = c->d_tile_rows.as<uint32_t>();
+        n_row_tiles = c->n_tile_rows;
+        cnt_smem = ((size_t)cap * cnt_bytes + 15) & ~(size_t)15;  // a tile uses at most `cap` counters
+    }
     const size_t smem = cnt_smem + kListCap * 2 + (top_n ? kListCap * 8 : 0);
 
     DistArgs a;
@@ -502,6 +556,7 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     a.tq = tq;
     a.tc = tc;
     a.n_col_tiles = n_col_tiles;
+    a.tile_rows = d_tile_rows;
     a.triangle = triangle;
     a.containment = containment;
     // distance of a zero cell is exactly 1.0 (dist.cpp:227-228): strict '<' for alldist, '<=' for dist
