@@ -213,3 +213,20 @@ def test_row_restricted_index_equals_full_index():
         assert np.array_equal(d, full_dict)
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("rows", [None, (1000, 3777)])
+def test_packed_triangle_tiles_equal_oracle(ctx, rows):
+    """alldist with one column tile packs the triangle: a tile holds only the columns right of its first row, so tiles
+    further down take more rows (4 ... 32).  4,800 small sketches give tiles of every height; whole triangle and a row block."""
+    h, off = synth.synth_sketches(7321, 800, 6, 48, 28)
+    n = len(off) - 1
+    sizes = np.diff(off).astype(np.int64)
+    ctx.set_params(10, 6, 3, util.shuffled_dim(10, 6, 3))
+    ctx.index_build(h, off)
+    for D, cont in ((0.12, 0), (0.3, 1)):
+        hits = ctx.dist_rows(h, off, True, 20, D, cont, rows=rows)
+        hits, _, _ = api.refine_hits(hits, sizes, sizes, 20, D, True, cont)
+        hr, hc, hm = oracle.alldist(h, off, 20, D, cont, rows=rows)
+        o = np.lexsort((hits[:, 1], hits[:, 0]))
+        assert len(hr) > 2000 and np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1)), (D, cont)
