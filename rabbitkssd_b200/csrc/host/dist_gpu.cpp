@@ -249,8 +249,7 @@ struct GpuPool {
         const bool cached = cache.valid && cache.use64 == use64 && cache.index_file == indexFile && cache.dict_file == dictFile &&
                             cache.n_genomes == ref_sizes.size();
         const size_t G = std::max<size_t>(1, std::min(want, kssd_host::device_count()));
-        ctx.resize(G);
-        for (size_t g = 0; g < G; g++) ctx[g] = kssd_host::context_at(g);
+        ctx = kssd_host::contexts_up_to(G);
         IndexFiles ix;
         if (cached) {
             std::cerr << "-----" << who << ": the index built by transSketches is still on the device, " << indexFile << " is not read back" << std::endl;
@@ -314,13 +313,6 @@ void group_by_row(std::vector<kssd_hit> &hits, size_t r0, size_t r1, std::vector
     for (size_t r = 0; r < r1 - r0; r++) row_begin[r + 1] += row_begin[r];
 }
 
-// another GPU is brought in (context, copy of the index) only when it gets at least this many query rows
-inline size_t min_rows_per_gpu(size_t dflt) {
-    const char *e = getenv("KSSD_B200_MIN_ROWS_PER_GPU");
-    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : dflt;
-    return v ? v : 1;
-}
-
 // GPU g of G owns the sub-files [first, first + count) of the numThreads the reference would write
 inline void files_of_gpu(size_t g, size_t G, int numThreads, int &first, int &count) {
     first = (int)(g * (size_t)numThreads / G);
@@ -340,7 +332,9 @@ void index_tridist(vector<sketch_t> &sketches, sketchInfo_t &info, string refSke
     flatten(sketches, use64, fl);
     const std::vector<uint32_t> &sizes = fl.sizes;
     GpuPool pool;
-    pool.setup(std::min<size_t>((size_t)numThreads, std::max<size_t>(1, numRef / min_rows_per_gpu(64))), use64, refSketchOut, "index_tridist()", sizes, fl);
+    // 100,000 sketches (5e9 cells) take 0.12 s on one B200: more GPUs only for jobs that are worth their start-up cost
+    pool.setup(std::min<size_t>((size_t)numThreads, kssd_host::gpus_for((double)numRef * (double)numRef / 2.0, 2e10, "KSSD_B200_CELLS_PER_GPU")), use64,
+               refSketchOut, "index_tridist()", sizes, fl);
     const size_t G = pool.ctx.size();
     const double t1 = get_sec();
     std::cerr << "===================time of read index and offset sketch file is: " << t1 - t0 << std::endl;
@@ -409,7 +403,8 @@ void index_dist(vector<sketch_t> &ref_sketches, sketchInfo_t &ref_info, string r
     flatten(query_sketches, use64, qfl);
     const std::vector<uint32_t> &rsizes = rfl.sizes, &qsizes = qfl.sizes;
     GpuPool pool;
-    pool.setup(std::min<size_t>((size_t)numThreads, std::max<size_t>(1, numQuery / min_rows_per_gpu(16))), use64, refSketchOut, "index_dist()", rsizes, qfl);
+    pool.setup(std::min<size_t>((size_t)numThreads, kssd_host::gpus_for((double)numQuery * (double)numRef, 2e10, "KSSD_B200_CELLS_PER_GPU")), use64,
+               refSketchOut, "index_dist()", rsizes, qfl);
     const size_t G = pool.ctx.size();
     const double t1 = get_sec();
     std::cerr << "===================time of read the index and dict sketch file is: " << t1 - t0 << std::endl;

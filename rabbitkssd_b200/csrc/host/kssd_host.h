@@ -62,25 +62,53 @@ inline const std::vector<int> &device_ids(bool fatal = true) {
     return ids;
 }
 inline size_t device_count() { return device_ids().size(); }
-// contexts are created on first use: a job that needs one GPU initialises one
+// contexts are created on first use: a job that needs one GPU initialises one.  Slots have their own locks, so several
+// contexts can be created at the same time (contexts_up_to).
+struct ContextSlot {
+    std::mutex mu;
+    kssd_ctx *ctx = nullptr;
+};
 inline kssd_ctx *context_at(size_t i, bool fatal = true) {
     static std::mutex mu;
-    static std::vector<kssd_ctx *> pool;
+    static std::vector<ContextSlot *> pool;
     const std::vector<int> &ids = device_ids(fatal);
-    std::lock_guard<std::mutex> lock(mu);
-    if (pool.size() < ids.size()) pool.resize(ids.size(), nullptr);
-    if (i >= pool.size()) {
+    ContextSlot *slot = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        while (pool.size() < ids.size()) pool.push_back(new ContextSlot());
+        if (i < pool.size()) slot = pool[i];
+    }
+    if (!slot) {
         if (!fatal) return nullptr;
-        fprintf(stderr, "ERROR: libkssd_b200: device slot %zu of %zu\n", i, pool.size());
+        fprintf(stderr, "ERROR: libkssd_b200: device slot %zu of %zu\n", i, ids.size());
         exit(1);
     }
-    if (!pool[i] && kssd_b200_init(&pool[i], ids[i]) != KSSD_OK) {
-        pool[i] = nullptr;
+    std::lock_guard<std::mutex> lock(slot->mu);
+    if (!slot->ctx && kssd_b200_init(&slot->ctx, ids[i]) != KSSD_OK) {
+        slot->ctx = nullptr;
         if (!fatal) return nullptr;
         fprintf(stderr, "ERROR: libkssd_b200: %s\n", kssd_b200_last_error());
         exit(1);
     }
-    return pool[i];
+    return slot->ctx;
+}
+// the first G contexts, created concurrently (creating one takes ~1 s)
+inline std::vector<kssd_ctx *> contexts_up_to(size_t G) {
+    std::vector<kssd_ctx *> out(G, nullptr);
+    std::vector<std::thread> th;
+    for (size_t g = 1; g < G; g++) th.emplace_back([&out, g] { out[g] = context_at(g); });
+    if (G) out[0] = context_at(0);
+    for (std::thread &t : th) t.join();
+    return out;
+}
+// How many GPUs a job is worth: bringing one in costs ~1 s (context) plus a copy of the index, so another GPU is used only
+// per `per_gpu` units of work (bytes to sketch, cells to compare); `env` overrides per_gpu (tests force 2 GPUs with it).
+inline size_t gpus_for(double work, double per_gpu, const char *env) {
+    if (const char *e = getenv(env)) per_gpu = atof(e);
+    if (!(per_gpu > 0)) per_gpu = 1;
+    const double want = 1.0 + work / per_gpu;
+    const size_t have = device_count();
+    return want >= (double)have ? have : (size_t)want;
 }
 inline kssd_ctx *context() { return context_at(0); }
 

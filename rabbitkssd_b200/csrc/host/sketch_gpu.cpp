@@ -254,9 +254,11 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         tr0 = t;
     };
     // one context per GPU; file t (position in the size-descending list) goes to GPU t % G, which balances the bytes
-    const size_t G = std::max<size_t>(1, std::min(kssd_host::device_count(), n));
-    std::vector<kssd_ctx *> ctxs(G);
-    for (size_t g = 0; g < G; g++) ctxs[g] = kssd_host::context_at(g);
+    // one GPU takes text at PCIe speed (55 GB/s), far more than parser threads deliver: another GPU only per 64 GB of input
+    double total_bytes = 0;
+    for (const fileInfo_t &f : fileList) total_bytes += (double)f.fileSize;
+    const size_t G = std::max<size_t>(1, std::min(kssd_host::gpus_for(total_bytes, 64e9, "KSSD_B200_SKETCH_BYTES_PER_GPU"), n));
+    std::vector<kssd_ctx *> ctxs = kssd_host::contexts_up_to(G);
     lap("contexts");
 #pragma omp parallel for num_threads((int)G) schedule(static, 1)
     for (size_t g = 0; g < G; g++) {  // the table build walks all 16^half_subk entries: one host thread per context

@@ -295,7 +295,7 @@ def test_multi_gpu_cli_equals_reference(work):
         pytest.skip("needs 2 GPUs")
     d, ndir, rdir = work["d"], work["dirs"]["new"], work["dirs"]["ref"]
     shuf = os.path.join(d, "L3K10.shuf")
-    out = _run_env(NEW, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "mg", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all"})
+    out = _run_env(NEW, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "mg", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_SKETCH_BYTES_PER_GPU": "1000000"})
     one = _run_env(NEW, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "sg", "-t", "4"], ndir, {"KSSD_B200_DEVICE": "0"})
     a, b = _sketch_sets(os.path.join(ndir, "mg.sketch")), _sketch_sets(os.path.join(ndir, "sg.sketch"))
     assert sorted(a) == sorted(b) and all(np.array_equal(a[n], b[n]) for n in a)
@@ -310,11 +310,11 @@ def test_multi_gpu_cli_equals_reference(work):
         shutil.copy(os.path.join(rdir, "refs.sketch"), os.path.join(work["dirs"][tag], "m.sketch"))
         shutil.copy(os.path.join(rdir, "queries.sketch"), os.path.join(work["dirs"][tag], "mq.sketch"))
     _run(REF, ["alldist", "-i", "m.sketch", "-D", "0.5", "-o", "m.alldist", "-t", "4"], rdir)
-    _run_env(NEW, ["alldist", "-i", "m.sketch", "-D", "0.5", "-o", "m.alldist", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_MIN_ROWS_PER_GPU": "2"})
+    _run_env(NEW, ["alldist", "-i", "m.sketch", "-D", "0.5", "-o", "m.alldist", "-t", "4"], ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_CELLS_PER_GPU": "8"})
     assert sorted(formats.parse_dist_text(os.path.join(rdir, "m.alldist"))) == sorted(formats.parse_dist_text(os.path.join(ndir, "m.alldist")))
     for extra in (["-D", "0.3"], ["-N", "2"], []):
         _run(REF, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, rdir)
-        _run_env(NEW, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_MIN_ROWS_PER_GPU": "2"})
+        _run_env(NEW, ["dist", "-r", "m.sketch", "-q", "mq.sketch", "-o", "m.dist", "-t", "4"] + extra, ndir, {"KSSD_B200_DEVICES": "all", "KSSD_B200_CELLS_PER_GPU": "8"})
         assert sorted(formats.parse_dist_text(os.path.join(rdir, "m.dist"))) == sorted(formats.parse_dist_text(os.path.join(ndir, "m.dist")))
 
 
