@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--nccl-gather", action="store_true", help="N > 1: gather the sketch shards with one NCCL all-gather instead of peer-memory reads")
+    ap.add_argument("--peer-nccl-barrier", action="store_true", help="N > 1: one-element all-reduce between publish and pull (round 1) instead of the peer-memory flags")
     ap.add_argument("--index-sharded", action="store_true", help="N > 1: build the index sharded by hash range and all-gather the pieces")
     ap.add_argument("--index-replicated", action="store_true", help="N > 1: every rank builds the whole index (default: the index restricted to its own row block)")
     ap.add_argument("--phases", action="store_true", help="diagnostic: per-phase wall times (synchronised) on stderr after the timed runs")
@@ -323,7 +324,7 @@ def run_b200(args):
     r0, r1 = bounds[rank], bounds[rank + 1]
     state = {}
     if world > 1 and not args.nccl_gather:
-        state["peers"] = PeerGather(dist, ctx, n_local, gather_cap, rank, world)
+        state["peers"] = PeerGather(dist, ctx, n_local, gather_cap, rank, world, nccl_barrier=args.peer_nccl_barrier)
 
     phase_t = {}
 
@@ -450,6 +451,7 @@ def run_b200(args):
         torch.cuda.synchronize()
         return n
 
+    barrier()  # pinned allocation takes a different time on every rank: the peer gather waits for the slowest at most ~10 s
     step_e2e()
     barrier()
     e0.record(stream)

@@ -153,10 +153,13 @@ int kssd_b200_sketch_concat_device(kssd_ctx *ctx, const uint32_t *d_parts, uint6
  *   peer_init      allocates the two buffers ([n_local sizes | cap_hashes hashes] each) and returns their IPC
  *                  handles (2 x 64 bytes) for the caller to exchange (any transport; bench.py uses one all-gather);
  *   peer_connect   handles of all ranks in rank order (world x 128 bytes) -> peer mappings;
- *   sketch_publish after sketch_finish(_device): this rank's sketch -> its current buffer (asynchronous);
- *   sketch_gather_peers   after a cross-rank barrier ON THE STREAM (e.g. a one-element all-reduce) so that every
- *                  rank's publish has completed: concatenated CSR as kssd_b200_sketch_concat_device returns it.
- * One barrier per step is enough: a buffer is rewritten two steps later, after a barrier its readers entered. */
+ *   sketch_publish after sketch_finish(_device): this rank's sketch -> its current buffer (asynchronous); the last CTA of
+ *                  the copy then stores this rank's publish count into its flag slot at EVERY rank (remote stores behind a
+ *                  system-scope fence) -- the barrier is part of the kernel, there is no collective in the step;
+ *   sketch_gather_peers   the concat kernels first wait (on the device) until every rank's flag has reached the current step,
+ *                  then read the peers' shards in place: concatenated CSR as kssd_b200_sketch_concat_device returns it.
+ *                  Every rank must publish once per step.  A peer that does not publish within ~10 s: KSSD_E_CUDA.
+ * A buffer is rewritten two steps later; by then every reader has passed the barrier of the step in between. */
 int kssd_b200_peer_init(kssd_ctx *ctx, uint32_t n_local, uint64_t cap_hashes, uint8_t *handles_out);
 int kssd_b200_peer_connect(kssd_ctx *ctx, const uint8_t *handles, uint32_t world, uint32_t rank);
 int kssd_b200_sketch_publish(kssd_ctx *ctx);

@@ -98,6 +98,7 @@ struct PeerState {
     uint32_t world = 0, rank = 0, n_local = 0;
     uint64_t stride = 0;  // u32 words per block: n_local sizes + capacity in hashes
     int flip = 0;
+    uint32_t step = 0;    // publishes so far: the value this rank writes into its flag at every peer (peer barrier, segsort.cu)
     uint32_t *own[2] = {nullptr, nullptr};
     uint32_t *peer[2][kMaxPeers] = {};
 };

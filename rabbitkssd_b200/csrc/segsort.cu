@@ -268,28 +268,60 @@ int genome_sort_unique(kssd_ctx *c, const uint64_t *d_emit, uint64_t n_emit, uin
 // sizes -> counts (one array), segment_scan_kernel -> offsets, one CTA per genome copies its hashes.
 struct PartTable { const uint32_t *p[kMaxPeers]; };
 
-__global__ void __launch_bounds__(256) concat_counts_kernel(const PartTable parts, uint32_t n_local, uint32_t n_total, uint32_t *__restrict__ counts) {
-    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g < n_total) counts[g] = parts.p[g / n_local][g % n_local];
+// Peer barrier without a collective: after its shard is complete, rank r stores its publish count into slot r of the flag
+// array of EVERY rank (remote stores over NVLink, behind a system-scope fence); a reader spins on its OWN flag array until
+// all slots have reached the step it is about to read.  flags == nullptr: the caller has synchronised the ranks already.
+__device__ __forceinline__ void peer_wait(const volatile uint32_t *flags, uint32_t world, uint32_t step, unsigned long long *result) {
+    if (flags && threadIdx.x == 0) {
+        const long long t0 = clock64();
+        for (uint32_t r = 0; r < world; r++)
+            while ((int32_t)(flags[r] - step) < 0) {
+                if (clock64() - t0 > (20ll << 30)) {  // ~10 s: a peer died; the host reports it instead of hanging
+                    atomicMax(result + 1, 2ull);
+                    r = world;
+                    break;
+                }
+                __nanosleep(200);
+            }
+        __threadfence_system();
+    }
+    __syncthreads();
 }
 
-__global__ void __launch_bounds__(128) concat_copy_kernel(const PartTable parts, uint64_t stride, uint32_t n_local,
+__global__ void __launch_bounds__(256) concat_counts_kernel(const PartTable parts, uint32_t n_local, uint32_t n_total, uint32_t *__restrict__ counts,
+                                                            const uint32_t *flags, uint32_t world, uint32_t step, unsigned long long *result) {
+    peer_wait(flags, world, step, result);
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n_total) counts[g] = __ldcv(parts.p[g / n_local] + g % n_local);
+}
+
+// The hashes of rank r's genomes are one contiguous run both in its block and in the concatenated array (genome-major,
+// rank order): blockIdx.y = rank, the CTAs of a rank stride over its run with coalesced loads from the peer's memory.
+__global__ void __launch_bounds__(256) concat_copy_kernel(const PartTable parts, uint64_t stride, uint32_t n_local, uint32_t world,
                                                           const uint64_t *__restrict__ off, uint32_t *__restrict__ out,
                                                           unsigned long long *__restrict__ result /* [0] total, [1] overflow */) {
-    const uint32_t g = blockIdx.x;
-    const uint32_t r = g / n_local;
+    const uint32_t r = blockIdx.y;
     const uint64_t r0 = off[(uint64_t)r * n_local], r1 = off[(uint64_t)(r + 1) * n_local];
     if (r1 - r0 > stride - n_local) {  // the shard of rank r did not fit its block: nothing of it is copied
-        if (threadIdx.x == 0 && g % n_local == 0) atomicExch(result + 1, 1ull);
+        if (threadIdx.x == 0 && blockIdx.x == 0) atomicMax(result + 1, 1ull);
         return;
     }
-    const uint64_t g0 = off[g], g1 = off[g + 1];
-    const uint32_t *src = parts.p[r] + n_local + (g0 - r0);
-    for (uint64_t i = threadIdx.x; i < g1 - g0; i += blockDim.x) out[g0 + i] = src[i];
-    if (g == gridDim.x - 1 && threadIdx.x == 0) result[0] = g1;
+    const uint32_t *src = parts.p[r] + n_local;
+    const uint64_t n = r1 - r0, step = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * step < n; i += 4 * step) {  // four independent loads in flight per thread (NVLink latency)
+        const uint32_t a = __ldcv(src + i), b = __ldcv(src + i + step), c2 = __ldcv(src + i + 2 * step), d = __ldcv(src + i + 3 * step);
+        out[r0 + i] = a;
+        out[r0 + i + step] = b;
+        out[r0 + i + 2 * step] = c2;
+        out[r0 + i + 3 * step] = d;
+    }
+    for (; i < n; i += step) out[r0 + i] = __ldcv(src + i);
+    if (r == world - 1 && blockIdx.x == 0 && threadIdx.x == 0) result[0] = r1;
 }
 
-static int sketch_concat_table(kssd_ctx *c, const PartTable &parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow) {
+static int sketch_concat_table(kssd_ctx *c, const PartTable &parts, uint64_t stride, uint32_t n_local, uint32_t world, uint64_t *total, int *overflow,
+                               const uint32_t *d_flags = nullptr, uint32_t step = 0) {
     cudaStream_t st = c->stream;
     const uint32_t n_total = n_local * world;
     const uint64_t result_word = ((uint64_t)n_total + 1) & ~1ull;  // [counts n_total][pad][result: total, overflow (u64 each)]
@@ -298,15 +330,20 @@ static int sketch_concat_table(kssd_ctx *c, const PartTable &parts, uint64_t str
     KSSD_TRY(c->d_cat_hashes.reserve(std::max<uint64_t>((stride - n_local) * world, 1) * 4, st));  // upper bound: every block full
     unsigned long long *result = reinterpret_cast<unsigned long long *>(c->d_cat_counts.as<uint32_t>() + result_word);
     KSSD_CUDA(cudaMemsetAsync(result, 0, 16, st));
-    concat_counts_kernel<<<(n_total + 255) / 256, 256, 0, st>>>(parts, n_local, n_total, c->d_cat_counts.as<uint32_t>());
+    concat_counts_kernel<<<(n_total + 255) / 256, 256, 0, st>>>(parts, n_local, n_total, c->d_cat_counts.as<uint32_t>(), d_flags, world, step, result);
     segment_scan_kernel<<<1, 1024, 0, st>>>(c->d_cat_counts.as<uint32_t>(), n_total, c->d_cat_off.as<uint64_t>(), nullptr);
-    concat_copy_kernel<<<n_total, 128, 0, st>>>(parts, stride, n_local, c->d_cat_off.as<uint64_t>(), c->d_cat_hashes.as<uint32_t>(), result);
+    concat_copy_kernel<<<dim3((unsigned)std::max(1, c->sm_count * 4 / (int)world), world), 256, 0, st>>>(parts, stride, n_local, world, c->d_cat_off.as<uint64_t>(),
+                                                                                                         c->d_cat_hashes.as<uint32_t>(), result);
     KSSD_CUDA(cudaGetLastError());
     c->launches += 3;
     KSSD_TRY(c->h_scalar.reserve(64));
     KSSD_CUDA(cudaMemcpyAsync(c->h_scalar.p, result, 16, cudaMemcpyDeviceToHost, st));
     KSSD_CUDA(cudaStreamSynchronize(st));
     *total = c->h_scalar.as<uint64_t>()[0];
+    if (c->h_scalar.as<uint64_t>()[1] == 2) {
+        set_error("sketch_gather_peers: a peer did not publish its shard within ~10 s (peer barrier timed out)");
+        return KSSD_E_CUDA;
+    }
     *overflow = c->h_scalar.as<uint64_t>()[1] != 0;
     c->cat_total = *total;
     c->cat_n = *overflow ? 0 : n_total;
@@ -321,10 +358,21 @@ int sketch_concat(kssd_ctx *c, const uint32_t *d_parts, uint64_t stride, uint32_
 }
 
 // ---- peer buffers: every rank publishes its shard in its own memory, the others read it over NVLink ---------------
+struct FlagTable { uint32_t *p[kMaxPeers]; };  // slot `rank` of every rank's flag array
+
 __global__ void __launch_bounds__(256) publish_kernel(const uint32_t *__restrict__ hashes, const uint64_t *__restrict__ genome_off, uint32_t n_local,
-                                                      uint64_t n_copy, uint32_t *__restrict__ block) {
+                                                      uint64_t n_copy, uint32_t *__restrict__ block, uint32_t *done, const FlagTable flags, uint32_t world,
+                                                      uint32_t step) {
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_local + n_copy; i += (uint64_t)gridDim.x * blockDim.x)
         block[i] = i < n_local ? (uint32_t)(genome_off[i + 1] - genome_off[i]) : hashes[i - n_local];
+    // the last CTA to finish tells every rank that this shard is complete
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(done, 1u) == gridDim.x - 1) {
+        *done = 0;
+        __threadfence_system();
+        for (uint32_t r = 0; r < world; r++) *reinterpret_cast<volatile uint32_t *>(flags.p[r]) = step;
+    }
 }
 
 int peer_init(kssd_ctx *c, uint32_t n_local, uint64_t cap_hashes, uint8_t *handles_out) {
@@ -333,7 +381,9 @@ int peer_init(kssd_ctx *c, uint32_t n_local, uint64_t cap_hashes, uint8_t *handl
     ps.n_local = n_local;
     ps.stride = (uint64_t)n_local + cap_hashes;
     for (int b = 0; b < 2; b++) {
-        KSSD_CUDA(cudaMalloc(&ps.own[b], ps.stride * 4 + 16));  // plain cudaMalloc: the whole allocation is what an IPC handle maps
+        // [sizes | hashes | 16 spare bytes | flags: one u32 per rank | done counter]; plain cudaMalloc: the whole allocation is what an IPC handle maps
+        KSSD_CUDA(cudaMalloc(&ps.own[b], ps.stride * 4 + 16 + (kMaxPeers + 4) * 4));
+        KSSD_CUDA(cudaMemset(reinterpret_cast<uint8_t *>(ps.own[b]) + ps.stride * 4, 0, 16 + (kMaxPeers + 4) * 4));
         cudaIpcMemHandle_t h;
         KSSD_CUDA(cudaIpcGetMemHandle(&h, ps.own[b]));
         static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
@@ -374,11 +424,16 @@ int sketch_publish(kssd_ctx *c) {
     PeerState &ps = c->peers;
     if (!ps.world) { set_error("sketch_publish: peer_connect first"); return KSSD_E_ARG; }
     if (c->n_genomes != ps.n_local) { set_error("sketch_publish: %u genomes in the session, peer buffers hold %u", c->n_genomes, ps.n_local); return KSSD_E_ARG; }
+    if (c->hash64) { set_error("sketch_publish: the peer gather carries 32-bit hashes only"); return KSSD_E_UNSUPPORTED; }
     ps.flip ^= 1;  // double buffer: the peers may still be reading the previous step's block
+    ps.step++;
     const uint64_t n_copy = std::min<uint64_t>(c->sketch_total, ps.stride - ps.n_local);  // a larger shard shows as overflow at the readers
     const uint64_t n = ps.n_local + n_copy;
+    FlagTable ft;
+    for (uint32_t r = 0; r < kMaxPeers; r++) ft.p[r] = r < ps.world ? ps.peer[0][r] + ps.stride + 4 + ps.rank : nullptr;  // flags live behind buffer 0
     publish_kernel<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 8), 256, 0, c->stream>>>(c->d_hashes.as<uint32_t>(), c->d_genome_off.as<uint64_t>(),
-                                                                                                ps.n_local, n_copy, ps.own[ps.flip]);
+                                                                                                ps.n_local, n_copy, ps.own[ps.flip],
+                                                                                                ps.own[0] + ps.stride + 4 + kMaxPeers, ft, ps.world, ps.step);
     KSSD_CUDA(cudaGetLastError());
     c->launches++;
     return KSSD_OK;
@@ -390,7 +445,8 @@ int sketch_gather_peers(kssd_ctx *c, uint64_t *total, int *overflow) {
     if (!ps.world) { set_error("sketch_gather_peers: peer_connect first"); return KSSD_E_ARG; }
     PartTable t;
     for (uint32_t r = 0; r < kMaxPeers; r++) t.p[r] = r < ps.world ? ps.peer[ps.flip][r] : nullptr;
-    return sketch_concat_table(c, t, ps.stride, ps.n_local, ps.world, total, overflow);
+    // the concat kernels wait in place until every rank's flag says that its current shard is complete: no collective
+    return sketch_concat_table(c, t, ps.stride, ps.n_local, ps.world, total, overflow, ps.own[0] + ps.stride + 4, ps.step);
 }
 
 }  // namespace kssd

@@ -60,10 +60,11 @@ def rect_bounds(n_query, parts):
 class PeerGather:
     """Sketch gather over peer memory (NVLink through CUDA IPC) instead of an NCCL transfer: every rank publishes its
     shard in its own buffer and reads the others' in place while concatenating (kssd_b200_sketch_gather_peers).
-    torch.distributed only carries the 128-byte IPC handles once and a one-element all-reduce per step as the barrier."""
+    torch.distributed only carries the 128-byte IPC handles once; the per-step barrier is a flag every rank stores into its
+    peers' memory after publishing (no collective in the step at all)."""
 
-    def __init__(self, dist, ctx, n_local, cap, rank, world):
-        self.dist, self.ctx, self.world = dist, ctx, world
+    def __init__(self, dist, ctx, n_local, cap, rank, world, nccl_barrier=False):
+        self.dist, self.ctx, self.world, self.nccl_barrier = dist, ctx, world, nccl_barrier
         dev = torch.device("cuda", torch.cuda.current_device())
         mine = torch.frombuffer(bytearray(ctx.peer_init(n_local, cap)), dtype=torch.uint8).to(dev)
         every = torch.empty(128 * world, dtype=torch.uint8, device=dev)
@@ -76,8 +77,11 @@ class PeerGather:
         t0 = _tick("", time.perf_counter()) if TRACE is not None else 0.0
         self.ctx.sketch_publish()
         t0 = _tick("peer.publish", t0)
-        self.dist.all_reduce(self.token)  # barrier on the stream: every rank's publish precedes its contribution
-        t0 = _tick("peer.barrier", t0)
+        # the library's concat kernels wait on flags the peers store over NVLink when their shard is complete (segsort.cu:
+        # peer_wait); round 1 passed a one-element all-reduce here instead (kept behind nccl_barrier for comparison)
+        if self.nccl_barrier:
+            self.dist.all_reduce(self.token)
+            t0 = _tick("peer.barrier", t0)
         ph, po, total, overflow = self.ctx.sketch_gather_peers()
         _tick("peer.pull", t0)
         return None if overflow else (ph, po, total)

@@ -3,9 +3,11 @@
 Every rank sketches its own genomes on cuda:LOCAL_RANK, publishes the shard in its peer buffer and pulls the shards of all
 ranks through CUDA-IPC mappings (kssd_b200_peer_init / _peer_connect / _sketch_publish / _sketch_gather_peers); then builds
 the index, runs its block of triangle rows and the hit sets of all ranks are compared with the oracle on rank 0.
-torch.distributed (gloo, CPU) only carries the IPC handles, the barriers and the final hit lists."""
+torch.distributed (gloo, CPU) only carries the IPC handles and the final hit lists; the per-step barrier is the library's own
+(flags stored into the peers' memory by the publish kernel, awaited by the concat kernel)."""
 import os
 import sys
+import time
 
 import numpy as np
 
@@ -56,10 +58,10 @@ def main():
     seq_l, _, off_l = synth.pack_batch(mine)
     bounds = multigpu.triangle_bounds(n_total, world)
     for step in range(4):
+        if step % 2 == rank % 2:
+            time.sleep(0.05 * (1 + rank))  # skew the ranks: a reader must WAIT for the slower publishers (peer flags, no host barrier)
         ctx.sketch(seq_l, off_l)
         ctx.sketch_publish()
-        ctx.sync()
-        dist.barrier()  # every rank's publish has completed
         ph, po, total, overflow = ctx.sketch_gather_peers()
         assert not overflow and total == len(want_h), (total, len(want_h))
         got_h = dev_np(ph, total, "<i4", np.uint32)
