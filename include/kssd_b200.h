@@ -274,6 +274,18 @@ int kssd_b200_dist_rows_device64(kssd_ctx *ctx, const uint64_t *d_q_hashes, cons
                                  int kmer_size, double max_dist, int containment, const kssd_hit **d_hits,
                                  uint64_t *n_hits);
 
+/* ---- set algebra on sketches ----------------------------------------------------------
+ * The arithmetic of `rabbit_kssd union` (src/subCommand.cpp:307-543: OR every hash of every genome into a bitmap over the
+ * hash space, list the set bits) and `rabbit_kssd sub` (:545-794: drop from every query genome the hashes present in the
+ * reference sketches).  hash_bytes = 4 (uint32) or 8 (64-bit configuration); host pointers; results are library owned
+ * until the next call.
+ *   set_union     all hashes, any order, duplicates allowed -> the sorted distinct set (the order the bitmap scan gives);
+ *   set_subtract  query sketches (CSR) minus a SORTED DISTINCT reference set (e.g. set_union's output): CSR of the
+ *                 surviving hashes, their order inside a genome kept. */
+int kssd_b200_set_union(kssd_ctx *ctx, const void *hashes, uint64_t n, int hash_bytes, const void **set, uint64_t *n_set);
+int kssd_b200_set_subtract(kssd_ctx *ctx, const void *q_hashes, const uint64_t *q_off, uint32_t n_query, const void *ref_set,
+                           uint64_t n_ref, int hash_bytes, const void **hashes, const uint64_t **genome_off);
+
 /* ---- introspection for bench.py / tests ---------------------------------------------------------------- */
 /* Bracket the scan / count kernels with CUDA events on the ctx stream (off by default). */
 int kssd_b200_set_profiling(kssd_ctx *ctx, int on);

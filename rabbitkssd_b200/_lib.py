@@ -82,6 +82,9 @@ SYMBOLS = {
                                         C.c_int, C.c_int, C.c_double, C.c_int, SINK, C.c_void_p]),
     "kssd_b200_dist_rows_device64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                                C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_void_p), u64p]),
+    "kssd_b200_set_union": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), u64p]),
+    "kssd_b200_set_subtract": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_int,
+                                         C.POINTER(C.c_void_p), C.POINTER(u64p)]),
     "kssd_b200_launch_count": (C.c_uint64, [C.c_void_p]),
     "kssd_b200_scan_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p]),
     "kssd_b200_count_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p, u64p]),

@@ -309,6 +309,34 @@ class Context:
         check(self.lib.kssd_b200_index_adopt_device(self.h, n_uniq, total, n_ref, C.c_void_p(d_uniq_hash),
                                                     C.c_void_p(d_uniq_off), C.c_void_p(d_dict), C.c_void_p(d_ref_sizes)))
 
+    # ---- set algebra ----
+    def set_union(self, hashes):
+        """All hashes (uint32 or uint64, any order) -> the sorted distinct set (`rabbit_kssd union`)."""
+        hashes = np.ascontiguousarray(hashes)
+        dt = np.uint64 if hashes.dtype == np.uint64 else np.uint32
+        hashes = np.ascontiguousarray(hashes, dtype=dt)
+        out, n = C.c_void_p(), C.c_uint64()
+        check(self.lib.kssd_b200_set_union(self.h, C.c_void_p(hashes.ctypes.data), len(hashes), hashes.itemsize, C.byref(out), C.byref(n)))
+        if n.value == 0:
+            return np.zeros(0, dt)
+        return np.frombuffer((C.c_char * (n.value * hashes.itemsize)).from_address(out.value), dtype=dt).copy()
+
+    def set_subtract(self, q_hashes, q_off, ref_set):
+        """Query sketches (CSR) minus a sorted distinct reference set -> (hashes, genome_off) (`rabbit_kssd sub`)."""
+        ref_set = np.ascontiguousarray(ref_set)
+        dt = np.uint64 if ref_set.dtype == np.uint64 else np.uint32
+        ref_set = np.ascontiguousarray(ref_set, dtype=dt)
+        q_hashes = np.ascontiguousarray(q_hashes, dtype=dt)
+        q_off = np.ascontiguousarray(q_off, dtype=np.uint64)
+        nq = len(q_off) - 1
+        out, off = C.c_void_p(), _lib.u64p()
+        check(self.lib.kssd_b200_set_subtract(self.h, C.c_void_p(q_hashes.ctypes.data), C.c_void_p(q_off.ctypes.data), nq,
+                                              C.c_void_p(ref_set.ctypes.data), len(ref_set), ref_set.itemsize, C.byref(out), C.byref(off)))
+        goff = _np_from_ptr(off, nq + 1, np.uint64)
+        n = int(goff[-1])
+        h = np.frombuffer((C.c_char * (n * ref_set.itemsize)).from_address(out.value), dtype=dt).copy() if n else np.zeros(0, dt)
+        return h, goff
+
     # ---- distances ----
     def set_emit_zero_cells(self, on=True):
         check(self.lib.kssd_b200_set_emit_zero_cells(self.h, int(on)))

@@ -191,6 +191,10 @@ void kssd_b200_destroy(kssd_ctx *c) {
     }
     c->d_fa_scratch.release();
     c->d_tile_rows.release();
+    c->d_setop_in.release();
+    c->d_setop_tmp.release();
+    c->d_setop_out.release();
+    c->h_setop.release();
     c->h_tile_rows.release();
     c->d_filter.release();
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

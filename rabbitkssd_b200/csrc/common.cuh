@@ -195,6 +195,10 @@ struct kssd_ctx {
     uint64_t tile_key[4] = {0, 0, 0, 0};
     uint32_t n_tile_rows = 0;
 
+    // set algebra (setops.cu)
+    kssd::DevBuf d_setop_in, d_setop_tmp, d_setop_out;
+    kssd::HostBuf h_setop;
+
     kssd::TimedLaunches t_scan, t_count;
 };
 
@@ -239,6 +243,9 @@ int index_build_range(kssd_ctx *c, const uint32_t *d_hashes, const uint64_t *d_g
 int index_adopt_parts(kssd_ctx *c, const uint32_t *d_blocks, uint64_t block_words, uint32_t parts, const uint64_t *d_genome_off, uint32_t n_genomes,
                       int *overflow);
 int index_build_buckets(kssd_ctx *c, int64_t known_max_hash = -1);  // after d_uniq_hash / n_uniq are in place
+// setops.cu
+int set_union_host(kssd_ctx *c, const void *hashes, uint64_t n, int hash_bytes, uint64_t *n_out);
+int set_subtract_host(kssd_ctx *c, const void *q, const uint64_t *q_off, uint32_t n_q, const void *ref, uint64_t n_ref, int hash_bytes);
 // dist.cu
 int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
                      uint32_t row_begin, uint32_t row_end, int triangle, int kmer_size, double max_dist,

@@ -20,11 +20,11 @@ fi
 [ -f "$OBJ/kssd_main.o" ] || bash "$ROOT/oracle/build_ref.sh"
 mkdir -p "$OUT"
 CXX="${ORACLE_CXX:-/usr/bin/g++}"
-for f in sketch_gpu dist_gpu; do
+for f in sketch_gpu dist_gpu setops_gpu; do
   "$CXX" -std=c++14 -O2 -g -fopenmp -include cstdint -I"$REF/src" -I"$REF/RabbitFX/io" -I"$ROOT/include" -w \
       -c "$HERE/$f.cpp" -o "$OUT/$f.o"
 done
-"$CXX" -fopenmp -Wl,--allow-multiple-definition "$OUT/sketch_gpu.o" "$OUT/dist_gpu.o" "$OBJ"/kssd_*.o \
+"$CXX" -fopenmp -Wl,--allow-multiple-definition "$OUT/sketch_gpu.o" "$OUT/dist_gpu.o" "$OUT/setops_gpu.o" "$OBJ"/kssd_*.o \
     -L"$OBJ" -lrabbitfx -L"$PKG" -lkssd_b200 -Wl,-rpath,'$ORIGIN/..' -Wl,-rpath,/usr/local/cuda/lib64 \
     -lz -lpthread -o "$OUT/rabbit_kssd_b200"
 echo "built $OUT/rabbit_kssd_b200"

@@ -6,5 +6,6 @@
 #include "index.cu"
 #include "hash64.cu"
 #include "fasta.cu"
+#include "setops.cu"
 #include "dist.cu"
 #include "capi.cu"

@@ -374,3 +374,34 @@ def test_raw_fasta_text_path_equals_reference(work, tmp_path):
     want = _sketch_sets(os.path.join(work["dirs"]["ref"], "rawref2.sketch"))
     got = _sketch_sets(os.path.join(work["dirs"]["new"], "rawnew2.sketch"))
     assert sorted(got) == sorted(want) and all(np.array_equal(got[n], want[n]) for n in want)
+
+
+def test_union_and_sub_commands(work):
+    """`rabbit_kssd union` / `sub` (set algebra, src/subCommand.cpp:307-794) on the GPU: same .sketch content as the
+    reference -- union: one sketch "<file> merged sketches" with the ascending distinct hashes; sub: every query genome
+    without the hashes of the reference sketches (compared per genome as sets: the reference writes genomes in the order its
+    threads finish)."""
+    d, rdir, ndir = work["d"], work["dirs"]["ref"], work["dirs"]["new"]
+    shuf = os.path.join(d, "L3K10.shuf")
+    if not os.path.exists(os.path.join(rdir, "refs.sketch")):
+        _run(REF, ["sketch", "-L", shuf, "-i", os.path.join(d, "refs.list"), "-o", "refs", "-t", "4"], rdir)
+    if not os.path.exists(os.path.join(rdir, "queries.sketch")):
+        _run(REF, ["sketch", "-q", "-L", shuf, "-i", os.path.join(d, "queries.list"), "-o", "queries", "-t", "4"], rdir)
+    for tag in ("ref", "new"):
+        shutil.copy(os.path.join(rdir, "refs.sketch"), os.path.join(work["dirs"][tag], "u_in.sketch"))
+        shutil.copy(os.path.join(rdir, "queries.sketch"), os.path.join(work["dirs"][tag], "u_q.sketch"))
+    _both(work, ["union", "-i", "u_in.sketch", "-o", "u_out.sketch", "-t", "3"])
+    ia, na, sa = formats.read_sketch(os.path.join(rdir, "u_out.sketch"))
+    ib, nb, sb = formats.read_sketch(os.path.join(ndir, "u_out.sketch"))
+    assert ia == ib and na == nb == ["u_in.sketch merged sketches"]
+    assert len(sa[0]) > 500 and np.array_equal(sa[0], sb[0])
+    _both(work, ["sub", "--rs", "u_out.sketch", "--qs", "u_q.sketch", "-o", "s_out.sketch", "-t", "3"])
+    a = _sketch_sets(os.path.join(rdir, "s_out.sketch"))
+    b = _sketch_sets(os.path.join(ndir, "s_out.sketch"))
+    assert sorted(a) == sorted(b) and any(len(v) for v in a.values())
+    for n in a:
+        assert np.array_equal(a[n], b[n]), n
+    # subtracting the multi-genome reference file directly gives the same result as subtracting its union
+    _run(NEW, ["sub", "--rs", "u_in.sketch", "--qs", "u_q.sketch", "-o", "s_out2.sketch", "-t", "3"], ndir)
+    c = _sketch_sets(os.path.join(ndir, "s_out2.sketch"))
+    assert sorted(c) == sorted(b) and all(np.array_equal(c[n], b[n]) for n in b)

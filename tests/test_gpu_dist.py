@@ -230,3 +230,31 @@ def test_packed_triangle_tiles_equal_oracle(ctx, rows):
         hr, hc, hm = oracle.alldist(h, off, 20, D, cont, rows=rows)
         o = np.lexsort((hits[:, 1], hits[:, 0]))
         assert len(hr) > 2000 and np.array_equal(hits[o], np.stack([hr, hc, hm], axis=1)), (D, cont)
+
+
+@pytest.mark.parametrize("dtype,bits", [(np.uint32, 28), (np.uint64, 40)])
+def test_set_union_and_subtract(ctx, dtype, bits):
+    """kssd_b200_set_union / _set_subtract (the arithmetic of `rabbit_kssd union` / `sub`, src/subCommand.cpp:307-794)
+    against numpy: union = sorted distinct hashes; subtract = query sketches without the hashes of the reference set, order
+    inside a genome kept; empty inputs and empty genomes included."""
+    rng = np.random.default_rng(11)
+    ref = rng.integers(0, 1 << bits, 300000, dtype=np.uint64).astype(dtype)
+    ref[1000:2000] = ref[:1000]  # duplicates
+    got = ctx.set_union(ref)
+    assert got.dtype == dtype and np.array_equal(got, np.unique(ref))
+    assert len(ctx.set_union(np.zeros(0, dtype))) == 0
+    sizes = [0, 5, 1221, 0, 70000, 333]
+    qs = []
+    for i, n in enumerate(sizes):
+        own = rng.integers(0, 1 << bits, n, dtype=np.uint64).astype(dtype)
+        take = rng.choice(got, n // 2) if n else np.zeros(0, dtype)
+        q = np.concatenate([own, take])
+        rng.shuffle(q)  # unsorted on purpose: the order of the survivors must be kept
+        qs.append(q)
+    off = np.concatenate([[0], np.cumsum([len(q) for q in qs])]).astype(np.uint64)
+    h, goff = ctx.set_subtract(np.concatenate(qs), off, got)
+    for i, q in enumerate(qs):
+        want = q[~np.isin(q, got)]
+        assert np.array_equal(h[int(goff[i]):int(goff[i + 1])], want), i
+    h, goff = ctx.set_subtract(np.concatenate(qs), off, np.zeros(0, dtype))  # nothing to subtract
+    assert np.array_equal(h, np.concatenate(qs)) and np.array_equal(goff, off)
