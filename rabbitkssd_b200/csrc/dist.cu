@@ -23,6 +23,7 @@
 //  The device test is conservative (superset); the host recomputes with the reference's exact expressions.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -513,7 +514,11 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     const uint32_t *d_tile_rows = nullptr;
     size_t cnt_smem = ((size_t)tq * tc * cnt_bytes + 15) & ~(size_t)15;
     if (triangle && n_col_tiles == 1 && rows > 1) {
-        const uint32_t q_max = std::min<uint32_t>(32, std::max<uint32_t>(tq_fill, tq));
+        // rows per tile further down the triangle: measured (profiles/r02i, r02j) -- taller tiles mean fewer CTAs and a longer
+        // tail, and the kernel is bound by shared-memory wavefronts, not by per-tile latency
+        uint32_t q_max = tq;
+        if (const char *e = getenv("KSSD_B200_TILE_QMAX")) q_max = std::max(1, atoi(e));
+        q_max = std::min<uint32_t>(32, std::max<uint32_t>(q_max, 1));
         const uint64_t key[4] = {((uint64_t)row_begin << 32) | row_end, c->n_ref, cap, q_max};
         if (memcmp(key, c->tile_key, sizeof(key)) != 0 || c->d_tile_rows.p == nullptr) {
             std::vector<uint32_t> starts;
