@@ -26,8 +26,12 @@ def lib_is_fresh():
 
 
 def build_lib(force=False, verbose=False):
+    force = force or bool(os.environ.get("KSSD_B200_FORCE_BUILD"))
     if not force and lib_is_fresh():
+        print(f"[rabbitkssd_b200.build] {os.path.basename(LIB)} is newer than every source under csrc/ and include/: not recompiled "
+              "(KSSD_B200_FORCE_BUILD=1 forces nvcc)", file=sys.stderr)
         return LIB
+    print(f"[rabbitkssd_b200.build] nvcc -gencode arch=compute_100a,code=sm_100a -> {os.path.basename(LIB)}", file=sys.stderr)
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
            "-Xcompiler", "-fPIC,-O3", "--shared", "-cudart", "shared",
            "-o", LIB, os.path.join(CSRC, "kssd_b200.cu")]
