@@ -99,6 +99,20 @@ __global__ void __launch_bounds__(256) bucket_fill_kernel(const uint32_t *__rest
     for (uint32_t b = lo; b <= hi; b++) bucket[b] = u;
 }
 
+// Few distinct hashes (small inputs: the smoke test, config 1): the kernel above would let one thread fill up to
+// n_buckets / n_uniq entries serially; here every bucket finds its own entry by binary search instead.
+__global__ void __launch_bounds__(256) bucket_search_kernel(const uint32_t *__restrict__ uniq_hash, uint32_t n_uniq, int shift, uint32_t n_buckets,
+                                                            uint32_t *__restrict__ bucket) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > n_buckets) return;
+    uint32_t lo = 0, hi = n_uniq;  // first u with (uniq_hash[u] >> shift) >= b
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uniq_hash[mid] >> shift) < b) lo = mid + 1; else hi = mid;
+    }
+    bucket[b] = lo;
+}
+
 int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
     cudaStream_t st = c->stream;
     if (c->n_uniq >= (1ull << 32)) { set_error("index: more than 2^32 distinct hashes"); return KSSD_E_UNSUPPORTED; }
@@ -114,8 +128,12 @@ int index_build_buckets(kssd_ctx *c, int64_t known_max_hash) {
     c->bucket_shift = bits > kBucketBits ? bits - kBucketBits : 0;
     c->n_buckets = (mx >> c->bucket_shift) + 1;  // <= 2^kBucketBits
     KSSD_TRY(c->d_bucket.reserve(((uint64_t)c->n_buckets + 1) * 4, st));
-    bucket_fill_kernel<<<(unsigned)((c->n_uniq + 1 + 255) / 256), 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), (uint32_t)c->n_uniq, c->bucket_shift,
-                                                                               c->n_buckets, c->d_bucket.as<uint32_t>());
+    if (c->n_uniq * 4 < c->n_buckets)
+        bucket_search_kernel<<<(c->n_buckets + 1 + 255) / 256, 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), (uint32_t)c->n_uniq, c->bucket_shift, c->n_buckets,
+                                                                            c->d_bucket.as<uint32_t>());
+    else
+        bucket_fill_kernel<<<(unsigned)((c->n_uniq + 1 + 255) / 256), 256, 0, st>>>(c->d_uniq_hash.as<uint32_t>(), (uint32_t)c->n_uniq, c->bucket_shift,
+                                                                                   c->n_buckets, c->d_bucket.as<uint32_t>());
     KSSD_CUDA(cudaGetLastError());
     c->launches++;
     return KSSD_OK;
