@@ -64,7 +64,7 @@ class BatchFiller {
         const double t_in = get_sec();
         {
             std::unique_lock<std::mutex> lock(mu_);
-            if (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
+            while (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);  // (another thread may have replaced it meanwhile)
             if (!cur_) {
                 check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, need), 1 << 16), "batch_acquire");
                 cur_->n_bytes = 0;
@@ -105,7 +105,7 @@ class BatchFiller {
         size_t at;
         {
             std::unique_lock<std::mutex> lock(mu_);
-            if (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
+            while (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);  // (another thread may have replaced it meanwhile)
             if (!cur_) {
                 check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, need), 1 << 16), "batch_acquire");
                 cur_->n_bytes = 0;
@@ -148,16 +148,24 @@ class BatchFiller {
     static constexpr size_t kDirectBytes = 1u << 20;   // records at least this long go straight from the parser's buffer
 
   private:
-    void submit(std::unique_lock<std::mutex> &lock) {  // all slices of cur_ are reserved by now: wait for their copies
+    // The current batch is full: wait for the copies into its reserved slices, then hand it to the library.  The wait
+    // releases the lock, so several threads can arrive here for the SAME batch: the first one to see it drained submits it,
+    // the others notice that cur_ has moved on and return (they must not submit the next, half-empty batch).
+    void submit(std::unique_lock<std::mutex> &lock) {
         const double t0 = get_sec();
-        cv_.wait(lock, [&] { return writers_ == 0; });
+        const uint64_t mine = gen_;
+        cv_.wait(lock, [&] { return writers_ == 0 || gen_ != mine; });
+        if (gen_ != mine) return;
         const double t1 = get_sec();
         if (cur_->n_bytes) check(kssd_b200_batch_submit(ctx_, cur_), "batch_submit");
         cur_ = nullptr;
+        gen_++;
+        cv_.notify_all();
         t_drain_ += t1 - t0;
         t_submit_ += get_sec() - t0;
         n_submit_++;
     }
+    uint64_t gen_ = 0;  // batches submitted so far
     double t_reserve_ = 0, t_fill_ = 0, t_submit_ = 0, t_drain_ = 0;
     int n_submit_ = 0;
     kssd_ctx *ctx_;
