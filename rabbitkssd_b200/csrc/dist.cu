@@ -497,7 +497,7 @@ int dist_rows_device(kssd_ctx *c, const void *d_q_hashes, const uint64_t *d_q_of
     const uint32_t cnt_bytes = wide ? 4 : 2;
     const uint32_t top_n = c->max_neighbor > 0 && c->max_neighbor < kListCap ? (uint32_t)c->max_neighbor : 0;
     // counters + 8 KB list (+ 32 KB of sort keys for top-N) <= ~104 KB: two CTAs per SM
-    const uint32_t smem_budget = top_n ? 64 * 1024 : 96 * 1024;
+    const uint32_t smem_budget = top_n ? 64 * 1024 : 100 * 1024;  // 2 x (100 + 8) KB fit the 227 KB of an SM; 50,000 references (config 3) fit one column tile
     const uint32_t cap = smem_budget / cnt_bytes;
     uint32_t tc = std::min<uint32_t>(c->n_ref, cap);
     tc = (tc + 7) & ~7u;  // keep rows 16-byte aligned
