@@ -286,6 +286,18 @@ int kssd_b200_set_union(kssd_ctx *ctx, const void *hashes, uint64_t n, int hash_
 int kssd_b200_set_subtract(kssd_ctx *ctx, const void *q_hashes, const uint64_t *q_off, uint32_t n_query, const void *ref_set,
                            uint64_t n_ref, int hash_bytes, const void **hashes, const uint64_t **genome_off);
 
+/* set_subtract without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic
+ * as kssd_b200_set_subtract for 32-bit hashes, but every input and output is a DEVICE pointer supplied by the caller
+ * (d_out_hashes: room for n_hashes entries, d_out_off: n_query + 1 entries; n_hashes = q_off[n_query]) and the scratch is
+ * a fixed 16.25 MiB __device__ array inside the library (held by every GPU that loads it, until exit).
+ * Limits: n_hashes <= 4,194,304 and n_query <= 65,536 per call, larger sizes return KSSD_E_ARG.  The work is enqueued on
+ * the context's stream (kssd_b200_sync waits for it); no cudaMalloc / cudaFree / allocating routine is called.  All calls
+ * on a device share the array: calls that overlap on the GPU race -- serialise them (one stream, or sync between calls). */
+int kssd_b200_set_subtract_noalloc(kssd_ctx *ctx, const uint32_t *d_q_hashes, const uint64_t *d_q_off, uint32_t n_query,
+                                   uint64_t n_hashes, const uint32_t *d_ref_set, uint64_t n_ref, uint32_t *d_out_hashes,
+                                   uint64_t *d_out_off);
+
 /* ---- introspection for bench.py / tests ---------------------------------------------------------------- */
 /* Bracket the scan / count kernels with CUDA events on the ctx stream (off by default). */
 int kssd_b200_set_profiling(kssd_ctx *ctx, int on);

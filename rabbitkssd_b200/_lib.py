@@ -85,6 +85,8 @@ SYMBOLS = {
     "kssd_b200_set_union": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), u64p]),
     "kssd_b200_set_subtract": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_int,
                                          C.POINTER(C.c_void_p), C.POINTER(u64p)]),
+    "kssd_b200_set_subtract_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint64,
+                                                 C.c_void_p, C.c_void_p]),
     "kssd_b200_launch_count": (C.c_uint64, [C.c_void_p]),
     "kssd_b200_scan_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p]),
     "kssd_b200_count_kernel_time": (C.c_int, [C.c_void_p, f64p, u64p, u64p, u64p]),

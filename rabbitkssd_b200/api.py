@@ -337,6 +337,12 @@ class Context:
         h = np.frombuffer((C.c_char * (n * ref_set.itemsize)).from_address(out.value), dtype=dt).copy() if n else np.zeros(0, dt)
         return h, goff
 
+    def set_subtract_noalloc(self, d_q_hashes, d_q_off, n_query, n_hashes, d_ref_set, n_ref, d_out_hashes, d_out_off):
+        """set_subtract on caller-owned DEVICE buffers (raw addresses), scratch in the library's fixed __device__ array: nothing
+        is allocated.  At most 4,194,304 query hashes (uint32) in 65,536 genomes; enqueued on the context's stream."""
+        check(self.lib.kssd_b200_set_subtract_noalloc(self.h, C.c_void_p(d_q_hashes), C.c_void_p(d_q_off), int(n_query), int(n_hashes),
+                                                      C.c_void_p(d_ref_set), int(n_ref), C.c_void_p(d_out_hashes), C.c_void_p(d_out_off)))
+
     # ---- distances ----
     def set_emit_zero_cells(self, on=True):
         check(self.lib.kssd_b200_set_emit_zero_cells(self.h, int(on)))

@@ -9,3 +9,4 @@
 #include "setops.cu"
 #include "dist.cu"
 #include "capi.cu"
+#include "noalloc.cu"
