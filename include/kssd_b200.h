@@ -75,6 +75,7 @@ int kssd_b200_set_relax_guard(kssd_ctx *ctx, int on);
  * to that count: k-mers ending before first_emit are context only. */
 #define KSSD_SEG_IN_HEADER 1
 #define KSSD_SEG_MID_LINE 2
+#define KSSD_RAW_FASTQ 2
 typedef struct kssd_batch {
     uint8_t *seq;         /* pinned, library owned, capacity bytes */
     uint8_t *qual;        /* pinned, same layout; used only when the session was begun with has_qual */
@@ -96,8 +97,15 @@ typedef struct kssd_batch {
      * length of that prefix: k-mers ending inside it were already found by the previous slice.  Header lines become one
      * separator byte.  Text kseq would not
      * take as plain FASTA (a line starting with '+' after a header / sequence line) makes sketch_finish return
-     * KSSD_E_SYNTAX.  Not for sessions with quality. */
-    int raw_fasta;        /* filled by caller; batch_acquire resets it to 0 */
+     * KSSD_E_SYNTAX.  Not for sessions with quality.
+     * raw_fasta = KSSD_RAW_FASTQ: raw four-line FASTQ text, tokenised on the device (replaces kseq's FASTQ branch,
+     * src/kseq.h:201-213, and the per-read loops src/sketch.cpp:273-307, :779-825 keep their arithmetic in the scan); sessions
+     * with quality only.  A piece is a WHOLE NUMBER OF RECORDS ('@' line, sequence line, '+' line, quality line), ends with
+     * '\n' and is padded with 0x00 to a multiple of 32; seg_flags / seg_first are not read.  Reads never share k-mers, so
+     * slices of a large file need no context.  Text that kseq would parse differently from "line number modulo four"
+     * (multi-line records, sequence and quality of different lengths, a record line that does not begin with '@', stray 0x00)
+     * makes sketch_finish return KSSD_E_SYNTAX. */
+    int raw_fasta;        /* filled by caller (0, 1 or KSSD_RAW_FASTQ); batch_acquire resets it to 0 */
     uint8_t *seg_flags;   /* pinned, seg_capacity entries */
     uint32_t *seg_first;  /* pinned, seg_capacity entries */
 } kssd_batch;

@@ -139,6 +139,32 @@ class Context:
         bt.raw_fasta = 1
         check(self.lib.kssd_b200_batch_submit(self.h, b))
 
+    def submit_raw_fastq(self, pieces):
+        """One batch of RAW four-line FASTQ text, tokenised on the device (kssd_batch.raw_fasta = KSSD_RAW_FASTQ).  pieces: list of
+        (genome, text bytes holding whole records and ending with a newline); every piece is padded with 0x00 to a multiple of 32."""
+        sizes = [(len(t) + 31) // 32 * 32 for _, t in pieces]
+        total = sum(sizes)
+        b = C.POINTER(_lib.Batch)()
+        check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), total, len(pieces)))
+        bt = b.contents
+        buf = np.zeros(total, dtype=np.uint8)
+        off = np.zeros(len(pieces) + 1, dtype=np.uint64)
+        at = 0
+        for i, ((g, t), sz) in enumerate(zip(pieces, sizes)):
+            t = np.frombuffer(bytes(t), dtype=np.uint8) if not isinstance(t, np.ndarray) else t
+            buf[at:at + len(t)] = t
+            off[i] = at
+            bt.seg_genome[i] = g
+            at += sz
+        off[len(pieces)] = at
+        C.memmove(bt.seq, buf.ctypes.data, total)
+        C.memmove(bt.seg_off, off.ctypes.data, off.nbytes)
+        bt.n_bytes = total
+        bt.n_seg = len(pieces)
+        bt.first_emit = 0
+        bt.raw_fasta = 2
+        check(self.lib.kssd_b200_batch_submit(self.h, b))
+
     def acquire_batch(self, min_capacity, min_segments):
         b = C.POINTER(_lib.Batch)()
         check(self.lib.kssd_b200_batch_acquire(self.h, C.byref(b), min_capacity, min_segments))

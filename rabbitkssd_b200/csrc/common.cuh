@@ -210,6 +210,9 @@ int launch_scan(kssd_ctx *c, const uint8_t *d_seq, const uint8_t *d_qual, uint64
 // fasta.cu
 int fasta_tokenise(kssd_ctx *c, const uint8_t *d_raw, uint64_t n_raw, const uint64_t *d_seg_off, const uint8_t *d_seg_flags, const uint32_t *d_seg_first,
                    uint32_t n_seg, uint8_t *d_out, uint64_t *d_cseg_off, uint64_t *d_cseg_first, uint32_t *d_anomaly, uint64_t *out_bytes);
+// fastq.cu
+int fastq_tokenise(kssd_ctx *c, const uint8_t *d_raw, uint64_t n_raw, const uint64_t *d_seg_off, uint32_t n_seg, uint8_t *d_out_seq,
+                   uint8_t *d_out_qual, uint64_t *d_cseg_off, uint32_t *d_anomaly, uint64_t *out_bytes);
 int build_tables(kssd_ctx *c, const int32_t *shuffled_dim);
 // radix.cu
 int radix_sort_u64(kssd_ctx *c, uint64_t *d_keys, uint64_t *d_tmp, uint64_t n, int lo_bits_begin, int lo_bits_end,

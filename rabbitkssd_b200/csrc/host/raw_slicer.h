@@ -79,4 +79,15 @@ struct RawSlicer {
     }
 };
 
+// Raw four-line FASTQ text (fastq.cu takes pieces of WHOLE records): how many of the len bytes at p are whole records, i.e. the
+// offset just behind the last '\n' whose number is a multiple of four -- one counting pass and at most four memrchr calls.
+// 0: not even one whole record.
+inline size_t fastq_whole_records(const unsigned char *p, size_t len) {
+    size_t lines = 0;
+    for (size_t i = 0; i < len; i++) lines += p[i] == '\n';
+    const unsigned char *e = len ? static_cast<const unsigned char *>(memrchr(p, '\n', len)) : nullptr;
+    for (size_t skip = lines % 4; e && skip; skip--) e = e > p ? static_cast<const unsigned char *>(memrchr(p, '\n', (size_t)(e - p))) : nullptr;
+    return e ? (size_t)(e - p) + 1 : 0;
+}
+
 }  // namespace kssd_host

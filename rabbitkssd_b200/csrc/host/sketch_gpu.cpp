@@ -52,7 +52,7 @@ const unsigned char kSeparator = '\n';  // any non-ACGT byte resets the valid-ru
 // threads run in parallel; a batch is submitted once its last writer has finished.
 class BatchFiller {
   public:
-    BatchFiller(kssd_ctx *ctx, bool has_qual, bool raw = false) : ctx_(ctx), has_qual_(has_qual), raw_(raw) {}
+    BatchFiller(kssd_ctx *ctx, bool has_qual, int raw = 0) : ctx_(ctx), has_qual_(has_qual), raw_(raw) {}  // raw: 0 parsed records, 1 FASTA text, KSSD_RAW_FASTQ
 
     // RAW FASTA text (kssd_batch.raw_fasta, tokenised on the device): reserves a piece of prefix_len + n bytes (padded with
     // '\n' to a multiple of 32), copies the prefix and lets `fill` put the n text bytes in place -- outside the lock.
@@ -70,7 +70,7 @@ class BatchFiller {
                 cur_->n_bytes = 0;
                 cur_->n_seg = 0;
                 cur_->first_emit = 0;
-                cur_->raw_fasta = 1;
+                cur_->raw_fasta = raw_;
             }
             b = cur_;
             at = b->n_bytes;
@@ -95,6 +95,50 @@ class BatchFiller {
             t_fill_ += t_filled - t_got;
         }
         cv_.notify_all();
+    }
+
+    // RAW FASTQ text (kssd_batch.raw_fasta = KSSD_RAW_FASTQ, tokenised on the device): reserves n_max bytes rounded up to 32 and
+    // lets `fill` put text there -- outside the lock; fill returns how many of the bytes are WHOLE RECORDS (ending with '\n'), the
+    // rest of the slice becomes 0x00 padding.  Returns that count.
+    template <typename Fill>
+    size_t append_raw_records(uint32_t genome, size_t n_max, Fill &&fill) {
+        const size_t need = (n_max + 31) & ~(size_t)31;
+        kssd_batch *b;
+        size_t at;
+        const double t_in = get_sec();
+        {
+            std::unique_lock<std::mutex> lock(mu_);
+            while (cur_ && (cur_->n_bytes + need > cur_->capacity || cur_->n_seg == cur_->seg_capacity)) submit(lock);
+            if (!cur_) {
+                check(kssd_b200_batch_acquire(ctx_, &cur_, std::max(kBatchBytes, need), 1 << 16), "batch_acquire");
+                cur_->n_bytes = 0;
+                cur_->n_seg = 0;
+                cur_->first_emit = 0;
+                cur_->raw_fasta = raw_;
+            }
+            b = cur_;
+            at = b->n_bytes;
+            b->seg_off[b->n_seg] = at;
+            b->seg_genome[b->n_seg] = genome;
+            b->seg_flags[b->n_seg] = 0;
+            b->seg_first[b->n_seg] = 0;
+            b->n_seg++;
+            b->n_bytes += need;
+            b->seg_off[b->n_seg] = b->n_bytes;
+            writers_++;
+        }
+        const double t_got = get_sec();
+        const size_t used = std::min(fill(b->seq + at), n_max);
+        memset(b->seq + at + used, 0, need - used);
+        const double t_filled = get_sec();
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            writers_--;
+            t_reserve_ += t_got - t_in;
+            t_fill_ += t_filled - t_got;
+        }
+        cv_.notify_all();
+        return used;
     }
 
     // seq[0, n) (+ qual) of `genome`; when `terminate` one separator byte is appended after the bytes
@@ -139,7 +183,7 @@ class BatchFiller {
         std::unique_lock<std::mutex> lock(mu_);
         if (cur_) submit(lock);
         if (getenv("KSSD_B200_TRACE") && (t_fill_ > 0 || t_submit_ > 0))
-            std::cerr << "[kssd_b200 trace] filler(" << (raw_ ? "raw" : "parsed") << "): thread-seconds waiting to reserve " << t_reserve_ << ", copying " << t_fill_
+            std::cerr << "[kssd_b200 trace] filler(" << (raw_ == KSSD_RAW_FASTQ ? "raw fastq" : raw_ ? "raw" : "parsed") << "): thread-seconds waiting to reserve " << t_reserve_ << ", copying " << t_fill_
                       << "; submits " << n_submit_ << " took " << t_submit_ << " s, of which waiting for writers " << t_drain_ << std::endl;
     }
 
@@ -169,7 +213,8 @@ class BatchFiller {
     double t_reserve_ = 0, t_fill_ = 0, t_submit_ = 0, t_drain_ = 0;
     int n_submit_ = 0;
     kssd_ctx *ctx_;
-    bool has_qual_, raw_;
+    bool has_qual_;
+    int raw_;
     std::mutex mu_;
     std::condition_variable cv_;
     int writers_ = 0;  // slices reserved in cur_ whose copy has not finished
@@ -228,6 +273,46 @@ bool read_raw_fasta(int fd, uint64_t size, uint32_t genome, BatchFiller &filler)
     return ok;
 }
 
+// plain four-line FASTQ = not gzip and the first byte is '@'
+bool looks_like_plain_fastq(int fd) {
+    unsigned char b[2] = {0, 0};
+    return pread(fd, b, 2, 0) >= 1 && b[0] == '@';
+}
+
+// Plain FASTQ files: the text goes to the GPU as it is, in pieces of whole records (fastq.cu).  Reads never share k-mers
+// (src/sketch.cpp:273-283 restarts the run at every read), so the host keeps no context: it only finds the last fourth line
+// end of what it read -- one pass that counts '\n' -- and starts the next piece there.
+// -> false when the file cannot go this way (read error, a record longer than a piece, an incomplete last record): the caller
+// falls back to kseq for the whole job.
+bool read_raw_fastq(int fd, uint64_t size, uint32_t genome, BatchFiller &filler) {
+    const size_t piece = std::max<size_t>(raw_piece_bytes(), 4096);
+    uint64_t pos = 0;
+    while (pos < size) {
+        const size_t n = (size_t)std::min<uint64_t>(size - pos, piece);
+        const bool last = pos + n == size;
+        bool ok = true;
+        const size_t used = filler.append_raw_records(genome, n + 1, [&](unsigned char *dst) -> size_t {
+            size_t got = 0;
+            while (got < n) {
+                const ssize_t r = pread(fd, dst + got, n - got, (off_t)(pos + got));
+                if (r <= 0) { ok = false; return 0; }
+                got += (size_t)r;
+            }
+            size_t len = n;
+            if (last && dst[len - 1] != '\n') dst[len++] = '\n';  // the last line may lack its line end
+            const size_t whole = kssd_host::fastq_whole_records(dst, len);
+            if (last)  // what follows the last whole record must be nothing kseq would read (it skips to the next '@' / '>')
+                for (size_t i = whole; i < len; i++)
+                    if (dst[i] == '@' || dst[i] == '>') ok = false;
+            return whole;
+        });
+        if (!ok || used == 0) return false;
+        if (last) break;
+        pos += used;
+    }
+    return true;
+}
+
 bool by_size_desc(const fileInfo_t &a, const fileInfo_t &b) { return a.fileSize > b.fileSize; }  // cmpFile, sketch.cpp:39
 
 bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, const kssd_parameter_t &p, bool fastq,
@@ -276,7 +361,7 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     std::vector<BatchFiller *> fillers(G), raw_fillers(G);
     for (size_t g = 0; g < G; g++) {
         fillers[g] = new BatchFiller(ctxs[g], fastq);
-        raw_fillers[g] = new BatchFiller(ctxs[g], false, true);
+        raw_fillers[g] = new BatchFiller(ctxs[g], fastq, fastq ? KSSD_RAW_FASTQ : 1);
     }
     bool raw_failed = false;
     lap("set_params + sketch_begin");
@@ -284,12 +369,13 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
     if (numThreads < 1) numThreads = 1;
 #pragma omp parallel for num_threads(numThreads) schedule(dynamic)
     for (size_t t = 0; t < n; t++) {
-        if (allow_raw && !fastq) {  // plain FASTA text: straight to the GPU, tokenised there (fasta.cu)
+        if (allow_raw) {  // plain FASTA / four-line FASTQ text: straight to the GPU, tokenised there (fasta.cu, fastq.cu)
             const int fd = open(fileList[t].fileName.c_str(), O_RDONLY);
             if (fd < 0) err(errno, "cannot open the genome file: %s\n", fileList[t].fileName.c_str());
             struct stat st;
-            const bool plain = fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0 && looks_like_plain_fasta(fd);
-            if (plain && !read_raw_fasta(fd, (uint64_t)st.st_size, (uint32_t)t, *raw_fillers[t % G])) {
+            const bool plain = fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0 && (fastq ? looks_like_plain_fastq(fd) : looks_like_plain_fasta(fd));
+            if (plain && !(fastq ? read_raw_fastq(fd, (uint64_t)st.st_size, (uint32_t)t, *raw_fillers[t % G])
+                                 : read_raw_fasta(fd, (uint64_t)st.st_size, (uint32_t)t, *raw_fillers[t % G]))) {
 #pragma omp atomic write
                 raw_failed = true;
             }
@@ -349,8 +435,8 @@ bool sketch_files(const std::string &inputFile, bool isQuery, int numThreads, co
         delete raw_fillers[g];
     }
     for (size_t g = 0; g < G; g++) raw_failed |= rcs[g] == KSSD_E_SYNTAX;
-    if (raw_failed) {  // text that is not plain FASTA (or a read error): the host parser decides, as in the reference
-        std::cerr << "-----raw FASTA text was not accepted by the device tokeniser, parsing all files with kseq" << std::endl;
+    if (raw_failed) {  // text that is not plain FASTA / four-line FASTQ (or a read error): the host parser decides, as in the reference
+        std::cerr << "-----raw text was not accepted by the device tokeniser, parsing all files with kseq" << std::endl;
         return sketch_files(inputFile, isQuery, numThreads, p, fastq, leastQual, leastNumKmer, sketches, info, outputFile, false);
     }
     lap("flush + sketch_finish");

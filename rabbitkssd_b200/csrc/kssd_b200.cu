@@ -6,6 +6,7 @@
 #include "index.cu"
 #include "hash64.cu"
 #include "fasta.cu"
+#include "fastq.cu"
 #include "setops.cu"
 #include "dist.cu"
 #include "capi.cu"

@@ -15,6 +15,17 @@ int main(int argc, char **argv) {
     while ((r = fread(buf, 1, sizeof buf, f)) > 0) t.append(buf, r);
     fclose(f);
     const size_t piece = (size_t)atoll(argv[2]);
+    if (argc > 3 && std::string(argv[3]) == "fastq") {  // the cuts of the raw FASTQ reader: "<begin> <end of the whole records>" per piece
+        size_t pos = 0;
+        while (pos < t.size()) {
+            const size_t n = std::min(t.size() - pos, piece);
+            const size_t whole = kssd_host::fastq_whole_records((const unsigned char *)t.data() + pos, n);
+            printf("%zu %zu\n", pos, pos + whole);
+            if (whole == 0 || pos + n == t.size()) break;
+            pos += whole;
+        }
+        return 0;
+    }
     kssd_host::RawSlicer sl;
     size_t pos = 0;
     const size_t n = t.size();

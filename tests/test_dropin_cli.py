@@ -376,6 +376,54 @@ def test_raw_fasta_text_path_equals_reference(work, tmp_path):
     assert sorted(got) == sorted(want) and all(np.array_equal(got[n], want[n]) for n in want)
 
 
+def test_raw_fastq_text_path_equals_reference(work, tmp_path):
+    """Plain four-line FASTQ files go to the GPU as raw text (cut at record boundaries by the shim, tokenised by fastq.cu):
+    ragged and empty reads, CRLF, many records per 32-byte chunk, a last line without a line end, trailing blank lines, tiny pieces
+    (KSSD_B200_RAW_PIECE_BYTES) -- the hash sets must equal the reference's (kseq on the host; -t 1 keeps the reference off its
+    RabbitFX big-file branch, src/sketch.cpp:644-650).  A multi-line record makes the shim fall back to kseq for the whole job."""
+    import test_gpu_fastq as tq
+    d = work["d"]
+    fl, texts = tq._files()
+    r, q = tq.make_reads(11, [100] * 3000)
+    texts.append(tq.fastq_text(r, q)[:-1])         # the last line has no line end
+    r, q = tq.make_reads(12, [75] * 3000)
+    texts.append(tq.fastq_text(r, q) + b"\n\n")    # blank lines after the last record
+    files = []
+    for i, t in enumerate(texts):
+        p = str(tmp_path / f"raw{i}.fq")
+        with open(p, "wb") as f:
+            f.write(t)
+        files.append(p)
+    lst = str(tmp_path / "rawfq.list")
+    with open(lst, "w") as f:
+        f.write("\n".join(files) + "\n")
+    shuf = os.path.join(d, "L3K10.shuf")
+    args = ["sketch", "-q", "-L", shuf, "-i", lst, "-Q", "50", "-n", "1"]
+    _run(REF, args + ["-o", "fqref", "-t", "1"], work["dirs"]["ref"])
+    want = _sketch_sets(os.path.join(work["dirs"]["ref"], "fqref.sketch"))
+    assert sum(len(v) for v in want.values()) > 300
+    for env in ({}, {"KSSD_B200_RAW_PIECE_BYTES": "4099"}, {"KSSD_B200_RAW_PIECE_BYTES": "70001"}, {"KSSD_B200_NO_RAW_FASTA": "1"}):
+        out = _run_env(NEW, args + ["-o", "fqnew", "-t", "3"], work["dirs"]["new"], env)
+        got = _sketch_sets(os.path.join(work["dirs"]["new"], "fqnew.sketch"))
+        assert sorted(got) == sorted(want), env
+        for n in want:
+            assert np.array_equal(got[n], want[n]), (env, n)
+        assert "parsing all files with kseq" not in out
+    # a record with its sequence on two lines: kseq reads it, the device tokeniser refuses it
+    good, bad = tq._bad_texts()
+    badp = str(tmp_path / "multi.fq")
+    with open(badp, "wb") as f:
+        f.write(bad["two_line_seq"] * 40)
+    with open(lst, "a") as f:
+        f.write(badp + "\n")
+    _run(REF, args + ["-o", "fqref2", "-t", "1"], work["dirs"]["ref"])
+    out = _run(NEW, args + ["-o", "fqnew2", "-t", "3"], work["dirs"]["new"])
+    assert "parsing all files with kseq" in out
+    want = _sketch_sets(os.path.join(work["dirs"]["ref"], "fqref2.sketch"))
+    got = _sketch_sets(os.path.join(work["dirs"]["new"], "fqnew2.sketch"))
+    assert sorted(got) == sorted(want) and all(np.array_equal(got[n], want[n]) for n in want)
+
+
 def test_union_and_sub_commands(work):
     """`rabbit_kssd union` / `sub` (set algebra, src/subCommand.cpp:307-794) on the GPU: same .sketch content as the
     reference -- union: one sketch "<file> merged sketches" with the ascending distinct hashes; sub: every query genome
