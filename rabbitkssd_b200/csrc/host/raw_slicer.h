@@ -6,6 +6,7 @@
 #endif
 #include <algorithm>
 #include <cstddef>
+#include <cstdint>
 #include <cstring>
 
 #include "kssd_b200.h"
@@ -83,8 +84,15 @@ struct RawSlicer {
 // offset just behind the last '\n' whose number is a multiple of four -- one counting pass and at most four memrchr calls.
 // 0: not even one whole record.
 inline size_t fastq_whole_records(const unsigned char *p, size_t len) {
-    size_t lines = 0;
-    for (size_t i = 0; i < len; i++) lines += p[i] == '\n';
+    size_t lines = 0, i = 0;
+    for (; i + 8 <= len; i += 8) {  // eight bytes at a time: 0x80 in every byte that equals '\n', exactly
+        uint64_t x;
+        memcpy(&x, p + i, 8);
+        x ^= 0x0A0A0A0A0A0A0A0Aull;
+        const uint64_t z = ~(((x & 0x7F7F7F7F7F7F7F7Full) + 0x7F7F7F7F7F7F7F7Full) | x | 0x7F7F7F7F7F7F7F7Full);
+        lines += (size_t)__builtin_popcountll(z);
+    }
+    for (; i < len; i++) lines += p[i] == '\n';
     const unsigned char *e = len ? static_cast<const unsigned char *>(memrchr(p, '\n', len)) : nullptr;
     for (size_t skip = lines % 4; e && skip; skip--) e = e > p ? static_cast<const unsigned char *>(memrchr(p, '\n', (size_t)(e - p))) : nullptr;
     return e ? (size_t)(e - p) + 1 : 0;

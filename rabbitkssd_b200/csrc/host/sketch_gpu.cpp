@@ -228,9 +228,12 @@ class BatchFiller {
 // next piece so that k-mers across the cut are seen (kssd_batch.raw_fasta).  One thread reads one file front to back -- a
 // 3 Gbp genome moves at memory-copy speed instead of through kseq's byte loop (the reference uses RabbitFX's chunked
 // reader for such files, src/sketch.cpp:173-238, :380-450).
+// Piece size: a batch (64 MiB) takes reservations from all parser threads at once, but only until it is full -- with 16 MiB
+// pieces three or four threads filled a batch while the others waited for the next one (20 GB of FASTQ moved at 4.9 GB/s,
+// profiles/r02x); 2 MiB gives every thread a slice in the open batch.
 size_t raw_piece_bytes() {
     const char *e = getenv("KSSD_B200_RAW_PIECE_BYTES");  // tests cut small files into many pieces
-    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(16u << 20);
+    const size_t v = e ? (size_t)strtoull(e, nullptr, 10) : (size_t)(2u << 20);
     return std::max<size_t>(v, 64);
 }
 
