@@ -192,21 +192,38 @@ __global__ void __launch_bounds__(kFaThreads) fa_classify_kernel(const FaArgs a)
     if (threadIdx.x == 0) a.tile_count[blockIdx.x] = total;
 }
 
+// The kept bytes of a tile, with the one separator that follows every piece that ends inside it, are contiguous in the
+// output: staged in shared memory (pre-filled with separators), written with 16-byte stores (store_tile_bytes).
 __global__ void __launch_bounds__(kFaThreads) fa_scatter_kernel(const FaArgs a) {
+    __shared__ __align__(16) uint8_t s_buf[kFaTile + kFaThreads + 16];  // at most one piece boundary per chunk
+    __shared__ uint32_t s_seg[2];
     const uint32_t c = blockIdx.x * kFaThreads + threadIdx.x;
-    if (c >= a.n_chunks) return;
-    uint32_t keep = a.chunk_keep[c];
-    if (!keep) return;
-    const uint4 *p = reinterpret_cast<const uint4 *>(a.raw + (uint64_t)c * kFaChunk);
-    const uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
-    const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    const bool live = c < a.n_chunks;
+    const uint32_t seg = live ? fa_segment_of(a, c) : 0;
+    const uint32_t n_live = min((uint32_t)kFaThreads, a.n_chunks - blockIdx.x * kFaThreads);
+    if (threadIdx.x == 0) s_seg[0] = seg;
+    if (threadIdx.x == n_live - 1) s_seg[1] = seg;
+    for (uint32_t v = threadIdx.x; v < sizeof(s_buf) / 16; v += blockDim.x) reinterpret_cast<uint4 *>(s_buf)[v] = make_uint4(0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au);
+    __syncthreads();
     // one separator follows every piece: pieces before this one shift the output by their number
-    uint8_t *o = a.out + a.tile_base[blockIdx.x] + a.chunk_pre[c] + fa_segment_of(a, c);
-    while (keep) {
-        const int i = __ffs(keep) - 1;
-        keep &= keep - 1;
-        *o++ = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+    uint8_t *out = a.out + a.tile_base[blockIdx.x] + s_seg[0];
+    const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(out) & 15u);
+    if (live) {
+        uint32_t keep = a.chunk_keep[c];
+        if (keep) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(a.raw + (uint64_t)c * kFaChunk);
+            const uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+            const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            uint8_t *o = s_buf + shift + a.chunk_pre[c] + (seg - s_seg[0]);
+            while (keep) {
+                const int i = __ffs(keep) - 1;
+                keep &= keep - 1;
+                *o++ = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+            }
+        }
     }
+    __syncthreads();
+    store_tile_bytes(s_buf, shift, a.tile_count[blockIdx.x] + (s_seg[1] - s_seg[0]), out);
 }
 
 // compacted piece table for the scan kernel

@@ -163,20 +163,35 @@ __global__ void __launch_bounds__(kFqThreads) fq_classify_kernel(const FqArgs a)
     }
 }
 
+// kept bytes go through shared memory and leave with 16-byte stores (store_tile_bytes, common.cuh)
 __global__ void __launch_bounds__(kFqThreads) fq_scatter_kernel(const FqArgs a) {
+    __shared__ __align__(16) uint8_t s_buf[kFqChunk * kFqThreads + 16];
     const uint32_t c = blockIdx.x * kFqThreads + threadIdx.x;
-    if (c >= a.n_chunks) return;
-    const uint32_t ks = a.keep_s[c], kq = a.keep_q[c];
-    if (!(ks | kq)) return;
+    const bool live = c < a.n_chunks;
+    uint32_t ks = 0, kq = 0, ps = 0, pq = 0;
     uint32_t w[8];
-    fq_load_bytes(a, c, w);
-    const uint64_t s0 = a.tile_base_s[blockIdx.x] + a.pre_s[c], q0 = a.tile_base_q[blockIdx.x] + a.pre_q[c];
-    uint8_t *o = a.out_s + s0;
+    if (live) {
+        ks = a.keep_s[c];
+        kq = a.keep_q[c];
+        ps = a.pre_s[c];
+        pq = a.pre_q[c];
+        if (ks | kq) fq_load_bytes(a, c, w);
+    }
+    const uint64_t s_base = a.tile_base_s[blockIdx.x], q_base = a.tile_base_q[blockIdx.x];
+    const uint32_t s_cnt = a.tile_cnt_s[blockIdx.x], q_cnt = a.tile_cnt_q[blockIdx.x];
+    // sequence bytes
+    uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(a.out_s + s_base) & 15u);
+    uint8_t *o = s_buf + shift + ps;
     for (uint32_t m = ks; m; m &= m - 1) {
         const int i = __ffs(m) - 1;
         *o++ = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
     }
-    o = a.out_q + q0;
+    __syncthreads();
+    store_tile_bytes(s_buf, shift, s_cnt, a.out_s + s_base);
+    __syncthreads();
+    // quality bytes + the per-record length check
+    shift = (uint32_t)(reinterpret_cast<uintptr_t>(a.out_q + q_base) & 15u);
+    o = s_buf + shift + pq;
     bool bad = false;
     for (uint32_t m = kq; m; m &= m - 1) {
         const int i = __ffs(m) - 1;
@@ -184,10 +199,12 @@ __global__ void __launch_bounds__(kFqThreads) fq_scatter_kernel(const FqArgs a) 
         *o++ = (uint8_t)b;
         if (b == '\n') {  // end of a record: as many quality bytes as sequence bytes (both counts include the line's separator)
             const uint32_t below = (1u << i) - 1u;
-            bad |= s0 + __popc(ks & below) != q0 + __popc(kq & below) + 1;
+            bad |= s_base + ps + __popc(ks & below) != q_base + pq + __popc(kq & below) + 1;
         }
     }
     if (bad) atomicExch(a.anomaly, 1u);
+    __syncthreads();
+    store_tile_bytes(s_buf, shift, q_cnt, a.out_q + q_base);
 }
 
 // piece table of the outputs for the scan kernel + the batch-wide checks
